@@ -1,0 +1,429 @@
+// C ABI of libdeepgo_b200.so (include/deepgo.h): context, model container, staging, and the
+// step orchestration (eval() of train.lua:4-12 + SGD:step of optimizer.lua:24-27).
+#include "model.cuh"
+#include "../../include/deepgo.h"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+static thread_local char g_err[1024] = "";
+
+void dg_set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *dg_last_error(void) { return g_err; }
+extern "C" int dg_version(void) { return 100; }
+
+extern "C" int dg_device_count(int *out) {
+    DG_REQUIRE(out, "dg_device_count: out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { n = 0; cudaGetLastError(); }
+    *out = n;
+    return 0;
+}
+
+extern "C" int dg_ctx_create(int device, dg_ctx **out) {
+    DG_REQUIRE(out, "dg_ctx_create: out is NULL");
+    int ndev = 0;
+    DG_CUDA(cudaGetDeviceCount(&ndev));
+    DG_REQUIRE(device >= 0 && device < ndev, "dg_ctx_create: device %d out of range (%d visible); there is no CPU fallback", device, ndev);
+    cudaDeviceProp prop;
+    DG_CUDA(cudaGetDeviceProperties(&prop, device));
+    DG_REQUIRE(prop.major == 10, "dg_ctx_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+    DG_CUDA(cudaSetDevice(device));
+    dg_ctx *c = new dg_ctx();
+    c->dev = device;
+    DG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    DG_CUDA(cudaEventCreate(&c->t0));
+    DG_CUDA(cudaEventCreate(&c->t1));
+    *out = c;
+    return 0;
+}
+
+extern "C" int dg_ctx_destroy(dg_ctx *c) {
+    if (!c) return 0;
+    cudaSetDevice(c->dev);
+    cudaStreamSynchronize(c->stream);
+    if (c->scratch) cudaFree(c->scratch);
+    if (c->flush_buf) cudaFree(c->flush_buf);
+    cudaEventDestroy(c->t0);
+    cudaEventDestroy(c->t1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return 0;
+}
+
+extern "C" int dg_ctx_synchronize(dg_ctx *c) {
+    DG_REQUIRE(c, "dg_ctx_synchronize: ctx is NULL");
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int dg_ctx_launch_count(dg_ctx *c, long long *out) {
+    DG_REQUIRE(c && out, "dg_ctx_launch_count: NULL argument");
+    *out = c->launches;
+    return 0;
+}
+
+extern "C" int dg_timer_start(dg_ctx *c) {
+    DG_REQUIRE(c, "dg_timer_start: ctx is NULL");
+    DG_CUDA(cudaEventRecord(c->t0, c->stream));
+    return 0;
+}
+extern "C" int dg_timer_stop(dg_ctx *c, float *ms) {
+    DG_REQUIRE(c && ms, "dg_timer_stop: NULL argument");
+    DG_CUDA(cudaEventRecord(c->t1, c->stream));
+    DG_CUDA(cudaEventSynchronize(c->t1));
+    DG_CUDA(cudaEventElapsedTime(ms, c->t0, c->t1));
+    return 0;
+}
+
+extern "C" int dg_ctx_flush_l2(dg_ctx *c) {
+    DG_REQUIRE(c, "dg_ctx_flush_l2: ctx is NULL");
+    DG_CUDA(cudaSetDevice(c->dev));
+    if (!c->flush_buf) {
+        c->flush_bytes = (size_t)256 << 20;       // > 126 MB L2
+        DG_CUDA(cudaMalloc(&c->flush_buf, c->flush_bytes));
+    }
+    return dg_launch_fill(c, (float *)c->flush_buf, c->flush_bytes / 4, 0.f);
+}
+
+int dg_ctx_scratch(dg_ctx *c, size_t bytes, void **out) {
+    if (bytes > c->scratch_bytes) {
+        DG_CUDA(cudaStreamSynchronize(c->stream));
+        if (c->scratch) DG_CUDA(cudaFree(c->scratch));
+        c->scratch = nullptr;
+        c->scratch_bytes = 0;
+        DG_CUDA(cudaMalloc(&c->scratch, bytes));
+        c->scratch_bytes = bytes;
+    }
+    *out = c->scratch;
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// encode (stand-alone, host buffers)
+// ---------------------------------------------------------------------------------------------
+static int check_records(const uint8_t *player, const uint8_t *rank, const uint8_t *sym, int n) {
+    for (int i = 0; i < n; ++i) {
+        DG_REQUIRE(player[i] == 1 || player[i] == 2, "record %d: player %d not in {1,2}", i, player[i]);
+        // dataloader.lua:87 indexes input[RANK+rank]: rank outside 1..9 is out of range there
+        DG_REQUIRE(rank[i] >= 1 && rank[i] <= 9, "record %d: rank %d outside 1..9 (dataloader.lua:87 would index out of range)", i, rank[i]);
+        DG_REQUIRE(!sym || sym[i] < 8, "record %d: symmetry id %d outside 0..7", i, sym[i]);
+    }
+    return 0;
+}
+
+extern "C" int dg_encode(dg_ctx *c, const uint8_t *raw, const uint8_t *player, const uint8_t *rank, const uint8_t *sym,
+                         int n, void *out, int outfmt) {
+    DG_REQUIRE(c, "dg_encode: ctx is NULL");
+    DG_REQUIRE(n >= 0, "dg_encode: n < 0");
+    if (n == 0) return 0;
+    DG_REQUIRE(raw && player && rank && out, "dg_encode: NULL buffer");
+    DG_REQUIRE(outfmt == DG_FMT_F32_NCHW || outfmt == DG_FMT_BITPLANES, "dg_encode: unknown output format %d", outfmt);
+    if (int rc = check_records(player, rank, sym, n)) return rc;
+    DG_CUDA(cudaSetDevice(c->dev));
+    const size_t raw_b = (size_t)n * DG_RAW_PLANES * DG_POINTS;
+    const size_t meta_off = (raw_b + 255) / 256 * 256;
+    const size_t out_off = (meta_off + 3 * (size_t)n + 255) / 256 * 256;
+    const size_t out_b = outfmt == DG_FMT_F32_NCHW ? (size_t)n * DG_PLANES * DG_POINTS * 4 : (size_t)n * DG_PLANES * 12 * 4;
+    char *d = nullptr;
+    if (int rc = dg_ctx_scratch(c, out_off + out_b, (void **)&d)) return rc;
+    uint8_t *d_raw = (uint8_t *)d, *d_pl = (uint8_t *)d + meta_off, *d_rk = d_pl + n, *d_sym = d_rk + n;
+    DG_CUDA(cudaMemcpyAsync(d_raw, raw, raw_b, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(d_pl, player, n, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(d_rk, rank, n, cudaMemcpyHostToDevice, c->stream));
+    if (sym) DG_CUDA(cudaMemcpyAsync(d_sym, sym, n, cudaMemcpyHostToDevice, c->stream));
+    int rc = outfmt == DG_FMT_F32_NCHW ? dg_launch_encode_f32(c, d_raw, d_pl, d_rk, sym ? d_sym : nullptr, n, (float *)(d + out_off))
+                                       : dg_launch_encode_bits(c, d_raw, d_pl, d_rk, sym ? d_sym : nullptr, n, (uint32_t *)(d + out_off));
+    if (rc) return rc;
+    DG_CUDA(cudaMemcpyAsync(out, d + out_off, out_b, cudaMemcpyDeviceToHost, c->stream));
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int dg_encode_labels(const uint8_t *x, const uint8_t *y, const uint8_t *sym, int n, int32_t *out) {
+    DG_REQUIRE(n >= 0, "dg_encode_labels: n < 0");
+    if (n == 0) return 0;
+    DG_REQUIRE(x && y && out, "dg_encode_labels: NULL buffer");
+    for (int i = 0; i < n; ++i) {
+        DG_REQUIRE(x[i] >= 1 && x[i] <= 19 && y[i] >= 1 && y[i] <= 19, "move %d: (%d,%d) outside the board", i, x[i], y[i]);
+        DG_REQUIRE(!sym || sym[i] < 8, "move %d: symmetry id %d outside 0..7", i, sym[i]);
+        int a = x[i] - 1, b = y[i] - 1;
+        const int s = sym ? sym[i] : 0;
+        if (s & 1) { int t = a; a = b; b = t; }
+        if (s & 2) a = 18 - a;
+        if (s & 4) b = 18 - b;
+        out[i] = 19 * a + b;
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// model
+// ---------------------------------------------------------------------------------------------
+extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int in_planes, int k_first, int precision,
+                               int max_batch, dg_model **out) {
+    DG_REQUIRE(c && out, "dg_model_create: NULL argument");
+    DG_REQUIRE(num_layers >= 2, "dg_model_create: numLayers must be >= 2");
+    DG_REQUIRE(channel_size >= 1 && max_batch >= 1, "dg_model_create: bad channelSize/max_batch");
+    DG_REQUIRE(k_first == 3 || k_first == 5, "dg_model_create: first kernel must be 3 or 5");
+    DG_REQUIRE(in_planes == DG_PLANES, "dg_model_create: in_planes must be %d (dataloader.lua TOTAL)", DG_PLANES);
+    DG_REQUIRE(precision == DG_PREC_FP32 || precision == DG_PREC_BF16, "dg_model_create: unknown precision %d", precision);
+    DG_CUDA(cudaSetDevice(c->dev));
+    dg_model *m = new dg_model();
+    m->ctx = c; m->L = num_layers; m->C = channel_size; m->in_planes = in_planes; m->k_first = k_first;
+    m->prec = precision; m->max_batch = max_batch;
+    size_t off = 0;
+    for (int l = 0; l < num_layers; ++l) {               // experiments.lua:88-93
+        LayerInfo li;
+        li.cin = l == 0 ? in_planes : channel_size;
+        li.cout = l == num_layers - 1 ? 1 : channel_size;
+        li.k = l == 0 ? k_first : 3;
+        li.nW = (size_t)li.cout * li.cin * li.k * li.k;
+        li.offW = off; off += li.nW;
+        li.offB = off; off += li.cout;
+        li.offA = off; off += (size_t)li.cout * DG_POINTS;
+        m->layers.push_back(li);
+    }
+    m->P = off;
+    const size_t B = max_batch;
+    DG_CUDA(cudaMalloc(&m->params, m->P * 4));
+    DG_CUDA(cudaMalloc(&m->grads, m->P * 4));
+    DG_CUDA(cudaMemsetAsync(m->params, 0, m->P * 4, c->stream));
+    DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));
+    DG_CUDA(cudaMalloc(&m->d_raw, B * DG_RAW_PLANES * DG_POINTS));
+    DG_CUDA(cudaMalloc(&m->d_player, B * 5));
+    m->d_rank = m->d_player + B; m->d_sym = m->d_rank + B; m->d_x = m->d_sym + B; m->d_y = m->d_x + B;
+    DG_CUDA(cudaMalloc(&m->d_targets, B * 4));
+    DG_CUDA(cudaMalloc(&m->d_argmax, B * 4));
+    DG_CUDA(cudaMalloc(&m->d_logp, B * DG_POINTS * 4));
+    DG_CUDA(cudaMalloc(&m->d_loss_n, B * 4));
+    DG_CUDA(cudaMalloc(&m->d_loss, 4));
+    DG_CUDA(cudaMalloc(&m->d_errors, 4));
+    m->act.assign(num_layers + 1, nullptr);
+    DG_CUDA(cudaMalloc(&m->act[0], B * in_planes * DG_POINTS * 4));
+    if (precision == DG_PREC_FP32) {
+        for (int l = 0; l < num_layers; ++l) DG_CUDA(cudaMalloc(&m->act[l + 1], B * m->layers[l].cout * DG_POINTS * 4));
+        for (int i = 0; i < 2; ++i) DG_CUDA(cudaMalloc(&m->dz[i], B * channel_size * DG_POINTS * 4));
+    } else {
+        if (int rc = dg_bf16_create(m)) { return rc; }
+    }
+    *out = m;
+    return 0;
+}
+
+extern "C" int dg_model_destroy(dg_model *m) {
+    if (!m) return 0;
+    cudaSetDevice(m->ctx->dev);
+    cudaStreamSynchronize(m->ctx->stream);
+    if (m->bf) dg_bf16_destroy(m);
+    for (float *p : m->act) if (p) cudaFree(p);
+    for (int i = 0; i < 2; ++i) if (m->dz[i]) cudaFree(m->dz[i]);
+    cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
+    cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
+    cudaFree(m->d_loss); cudaFree(m->d_errors);
+    delete m;
+    return 0;
+}
+
+extern "C" int dg_model_param_count(dg_model *m, size_t *out) {
+    DG_REQUIRE(m && out, "dg_model_param_count: NULL argument");
+    *out = m->P;
+    return 0;
+}
+
+extern "C" int dg_model_set_params(dg_model *m, const float *host, size_t n) {
+    DG_REQUIRE(m && host, "dg_model_set_params: NULL argument");
+    DG_REQUIRE(n == m->P, "dg_model_set_params: got %zu values, the model has %zu parameters", n, m->P);
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    DG_CUDA(cudaMemcpyAsync(m->params, host, n * 4, cudaMemcpyHostToDevice, m->ctx->stream));
+    if (m->bf) if (int rc = dg_bf16_params_changed(m)) return rc;
+    DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return 0;
+}
+extern "C" int dg_model_get_params(dg_model *m, float *host, size_t n) {
+    DG_REQUIRE(m && host, "dg_model_get_params: NULL argument");
+    DG_REQUIRE(n == m->P, "dg_model_get_params: buffer holds %zu values, the model has %zu parameters", n, m->P);
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    DG_CUDA(cudaMemcpyAsync(host, m->params, n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
+    DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return 0;
+}
+extern "C" int dg_model_get_grads(dg_model *m, float *host, size_t n) {
+    DG_REQUIRE(m && host, "dg_model_get_grads: NULL argument");
+    DG_REQUIRE(n == m->P, "dg_model_get_grads: buffer holds %zu values, the model has %zu parameters", n, m->P);
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    DG_CUDA(cudaMemcpyAsync(host, m->grads, n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
+    DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return 0;
+}
+extern "C" int dg_zero_grads(dg_model *m) {
+    DG_REQUIRE(m, "dg_zero_grads: model is NULL");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, m->ctx->stream));
+    return 0;
+}
+extern "C" int dg_model_set_global_batch(dg_model *m, int gb) {
+    DG_REQUIRE(m && gb >= 0, "dg_model_set_global_batch: bad argument");
+    m->global_batch = gb;
+    return 0;
+}
+
+extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
+                                      const uint8_t *sym, const uint8_t *x, const uint8_t *y, int n) {
+    DG_REQUIRE(m, "dg_model_set_batch_raw: model is NULL");
+    DG_REQUIRE(n >= 1 && n <= m->max_batch, "dg_model_set_batch_raw: batch %d outside 1..%d", n, m->max_batch);
+    DG_REQUIRE(raw && player && rank, "dg_model_set_batch_raw: NULL buffer");
+    DG_REQUIRE((x == nullptr) == (y == nullptr), "dg_model_set_batch_raw: x and y must both be given or both NULL");
+    if (int rc = check_records(player, rank, sym, n)) return rc;
+    dg_ctx *c = m->ctx;
+    DG_CUDA(cudaSetDevice(c->dev));
+    DG_CUDA(cudaMemcpyAsync(m->d_raw, raw, (size_t)n * DG_RAW_PLANES * DG_POINTS, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(m->d_player, player, n, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(m->d_rank, rank, n, cudaMemcpyHostToDevice, c->stream));
+    if (sym) DG_CUDA(cudaMemcpyAsync(m->d_sym, sym, n, cudaMemcpyHostToDevice, c->stream));
+    else DG_CUDA(cudaMemsetAsync(m->d_sym, 0, n, c->stream));
+    m->n = n; m->have_raw = true; m->forward_done = false;
+    m->have_targets = x != nullptr;
+    if (x) {
+        for (int i = 0; i < n; ++i)
+            DG_REQUIRE(x[i] >= 1 && x[i] <= 19 && y[i] >= 1 && y[i] <= 19, "move %d: (%d,%d) outside the board", i, x[i], y[i]);
+        DG_CUDA(cudaMemcpyAsync(m->d_x, x, n, cudaMemcpyHostToDevice, c->stream));
+        DG_CUDA(cudaMemcpyAsync(m->d_y, y, n, cudaMemcpyHostToDevice, c->stream));
+        if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
+    }
+    if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]);
+    return dg_bf16_stage_raw(m);
+}
+
+extern "C" int dg_model_set_batch_planes(dg_model *m, const float *planes, const int32_t *targets0, int n) {
+    DG_REQUIRE(m && planes, "dg_model_set_batch_planes: NULL argument");
+    DG_REQUIRE(n >= 1 && n <= m->max_batch, "dg_model_set_batch_planes: batch %d outside 1..%d", n, m->max_batch);
+    dg_ctx *c = m->ctx;
+    DG_CUDA(cudaSetDevice(c->dev));
+    if (targets0) {
+        for (int i = 0; i < n; ++i)
+            DG_REQUIRE(targets0[i] >= 0 && targets0[i] < DG_POINTS, "target %d: class %d outside 0..360", i, targets0[i]);
+        DG_CUDA(cudaMemcpyAsync(m->d_targets, targets0, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    DG_CUDA(cudaMemcpyAsync(m->act[0], planes, (size_t)n * m->in_planes * DG_POINTS * 4, cudaMemcpyHostToDevice, c->stream));
+    m->n = n; m->have_raw = false; m->have_targets = targets0 != nullptr; m->forward_done = false;
+    if (m->prec == DG_PREC_BF16) return dg_bf16_stage_planes(m);
+    return 0;
+}
+
+static float grad_scale(dg_model *m) { return 1.0f / (float)(m->global_batch > 0 ? m->global_batch : m->n); }
+
+// forward up to the ReLU'd last-layer map, then log-softmax (+ per-sample NLL, argmax)
+static int forward_impl(dg_model *m) {
+    dg_ctx *c = m->ctx;
+    DG_REQUIRE(m->n > 0, "forward: no batch staged (call dg_model_set_batch_* first)");
+    if (m->prec == DG_PREC_FP32) {
+        for (int l = 0; l < m->L; ++l) {
+            const LayerInfo &li = m->layers[l];
+            if (int rc = dg_simt_conv(c, m->act[l], m->params + li.offW, m->params + li.offB, m->params + li.offA, nullptr,
+                                      m->act[l + 1], m->n, li.cin, li.cout, li.k, 0, 1)) return rc;
+        }
+        if (int rc = dg_launch_logsoftmax_nll(c, m->act[m->L], m->have_targets ? m->d_targets : nullptr, m->d_logp, m->d_loss_n,
+                                              nullptr, m->d_argmax, m->n, 0.f)) return rc;
+    } else {
+        if (int rc = dg_bf16_forward(m)) return rc;
+    }
+    m->forward_done = true;
+    return 0;
+}
+
+static int backward_impl(dg_model *m) {
+    dg_ctx *c = m->ctx;
+    DG_REQUIRE(m->forward_done, "backward: call dg_forward first");
+    DG_REQUIRE(m->have_targets, "backward: the staged batch has no targets");
+    const float scale = grad_scale(m);
+    if (m->prec == DG_PREC_BF16) return dg_bf16_backward(m, scale);
+    int cur = 0;
+    if (int rc = dg_launch_logsoftmax_nll(c, m->act[m->L], m->d_targets, m->d_logp, m->d_loss_n, m->dz[cur], m->d_argmax, m->n, scale)) return rc;
+    for (int l = m->L - 1; l >= 0; --l) {
+        const LayerInfo &li = m->layers[l];
+        if (int rc = dg_simt_bias_grad(c, m->dz[cur], m->grads + li.offA, m->grads + li.offB, m->n, li.cout)) return rc;
+        if (int rc = dg_simt_wgrad(c, m->act[l], m->dz[cur], m->grads + li.offW, m->n, li.cin, li.cout, li.k)) return rc;
+        if (l > 0) {
+            // input gradient through the conv, then the ReLU mask of the layer below (h > 0 <=> z > 0)
+            if (int rc = dg_simt_conv(c, m->dz[cur], m->params + li.offW, nullptr, nullptr, m->act[l], m->dz[cur ^ 1], m->n,
+                                      li.cout, li.cin, li.k, 1, 0)) return rc;
+            cur ^= 1;
+        }
+    }
+    return 0;
+}
+
+static int read_loss(dg_model *m, float *loss_out, int *errors_out) {
+    dg_ctx *c = m->ctx;
+    if (int rc = dg_launch_loss_reduce(c, m->d_loss_n, m->d_argmax, m->d_targets, m->n, m->d_loss, m->d_errors)) return rc;
+    if (loss_out) DG_CUDA(cudaMemcpyAsync(loss_out, m->d_loss, 4, cudaMemcpyDeviceToHost, c->stream));
+    if (errors_out) DG_CUDA(cudaMemcpyAsync(errors_out, m->d_errors, 4, cudaMemcpyDeviceToHost, c->stream));
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int dg_forward(dg_model *m, float *logprobs_out) {
+    DG_REQUIRE(m, "dg_forward: model is NULL");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (int rc = forward_impl(m)) return rc;
+    if (logprobs_out) {
+        DG_CUDA(cudaMemcpyAsync(logprobs_out, m->d_logp, (size_t)m->n * DG_POINTS * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
+        DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    }
+    return 0;
+}
+
+extern "C" int dg_loss_backward(dg_model *m, float *loss_out) {
+    DG_REQUIRE(m, "dg_loss_backward: model is NULL");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (int rc = backward_impl(m)) return rc;
+    if (loss_out) return read_loss(m, loss_out, nullptr);
+    return 0;
+}
+
+extern "C" int dg_sgd_step(dg_model *m, float rate) {
+    DG_REQUIRE(m, "dg_sgd_step: model is NULL");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (int rc = dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate)) return rc;
+    if (m->bf) return dg_bf16_params_changed(m);
+    return 0;
+}
+
+extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
+    DG_REQUIRE(m, "dg_train_step: model is NULL");
+    dg_ctx *c = m->ctx;
+    DG_CUDA(cudaSetDevice(c->dev));
+    DG_REQUIRE(m->have_targets, "dg_train_step: the staged batch has no targets");
+    DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));          // train.lua:5
+    if (int rc = forward_impl(m)) return rc;                               // train.lua:6
+    if (int rc = backward_impl(m)) return rc;                              // train.lua:8-10
+    if (c->world > 1) if (int rc = dg_dp_allreduce(c, m->grads, m->P)) return rc;
+    if (int rc = dg_sgd_step(m, rate)) return rc;                          // train.lua:131
+    if (loss_out) return read_loss(m, loss_out, nullptr);
+    return 0;
+}
+
+extern "C" int dg_argmax(dg_model *m, int32_t *out) {
+    DG_REQUIRE(m && out, "dg_argmax: NULL argument");
+    DG_REQUIRE(m->forward_done, "dg_argmax: call dg_forward first");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    DG_CUDA(cudaMemcpyAsync(out, m->d_argmax, (size_t)m->n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
+    DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
+    return 0;
+}
+
+extern "C" int dg_eval_batch(dg_model *m, int *errors_out, float *cost_out) {
+    DG_REQUIRE(m, "dg_eval_batch: model is NULL");
+    DG_REQUIRE(m->have_targets, "dg_eval_batch: the staged batch has no targets");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (int rc = forward_impl(m)) return rc;
+    return read_loss(m, cost_out, errors_out);
+}

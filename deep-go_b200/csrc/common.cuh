@@ -1,0 +1,84 @@
+// Shared declarations for libdeepgo_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <vector>
+#include <string>
+
+#define DG_BOARD 19
+#define DG_POINTS 361
+#define DG_RAW_PLANES 9
+#define DG_PLANES 37
+
+void dg_set_error(const char *fmt, ...);
+
+#define DG_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            dg_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            return 1;                                                                              \
+        }                                                                                          \
+    } while (0)
+
+#define DG_REQUIRE(cond, ...)                                                                      \
+    do {                                                                                           \
+        if (!(cond)) {                                                                             \
+            dg_set_error(__VA_ARGS__);                                                             \
+            return 2;                                                                              \
+        }                                                                                          \
+    } while (0)
+
+struct dg_ctx {
+    int dev = 0;
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    // grow-only device scratch for the stand-alone entry points (dg_encode, dg_summarize_boards)
+    void *scratch = nullptr;
+    size_t scratch_bytes = 0;
+    void *flush_buf = nullptr;
+    size_t flush_bytes = 0;
+    // data parallel (dp.cu)
+    void *nccl_lib = nullptr;
+    void *comm = nullptr;
+    int rank = 0, world = 1;
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t ev_grad_ready = nullptr, ev_comm_done = nullptr;
+};
+
+struct LayerInfo {
+    int cin, cout, k;
+    size_t offW, offB, offA;   // offsets into the Torch7-order flat vector
+    size_t nW;
+};
+
+int dg_ctx_scratch(dg_ctx *ctx, size_t bytes, void **out);
+
+// ---- encode.cu
+int dg_launch_encode_f32(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
+                         const uint8_t *sym, int n, float *out);
+int dg_launch_encode_bits(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
+                          const uint8_t *sym, int n, uint32_t *out);
+int dg_launch_labels(dg_ctx *ctx, const uint8_t *x, const uint8_t *y, const uint8_t *sym, int n, int32_t *out);
+
+// ---- conv_simt.cu (fp32 reference-precision path, NCHW)
+int dg_simt_conv(dg_ctx *ctx, const float *in, const float *W, const float *b, const float *a, const float *mask,
+                 float *out, int n, int cin, int cout, int k, int transposed, int relu);
+int dg_simt_wgrad(dg_ctx *ctx, const float *x, const float *dz, float *gW, int n, int cin, int cout, int k);
+int dg_simt_bias_grad(dg_ctx *ctx, const float *dz, float *ga, float *gb, int n, int cout);
+
+// ---- head.cu (log-softmax + NLL + dlogits, argmax, loss reduction)
+int dg_launch_logsoftmax_nll(dg_ctx *ctx, const float *h_last, const int32_t *targets, float *logp, float *loss_n,
+                             float *dz_last, int32_t *argmax, int n, float scale);
+int dg_launch_loss_reduce(dg_ctx *ctx, const float *loss_n, const int32_t *argmax, const int32_t *targets, int n,
+                          float *loss_out, int *errors_out);
+
+// ---- sgd.cu
+int dg_launch_sgd(dg_ctx *ctx, float *p, const float *g, size_t n, float rate);
+int dg_launch_fill(dg_ctx *ctx, float *p, size_t n, float v);
+
+// ---- dp.cu
+int dg_dp_allreduce(dg_ctx *ctx, float *buf, size_t n);

@@ -1,0 +1,35 @@
+// dg_model: parameters in Torch7 flat order + per-precision activation storage.
+#pragma once
+#include "common.cuh"
+
+struct Bf16Path;   // conv_umma.cu
+
+struct dg_model {
+    dg_ctx *ctx = nullptr;
+    int L = 0, C = 0, in_planes = 37, k_first = 5, prec = 0, max_batch = 0;
+    size_t P = 0;
+    std::vector<LayerInfo> layers;
+    float *params = nullptr, *grads = nullptr;
+    // staged batch
+    int n = 0;
+    int global_batch = 0;
+    bool have_targets = false, have_raw = false, forward_done = false;
+    uint8_t *d_raw = nullptr, *d_player = nullptr, *d_rank = nullptr, *d_sym = nullptr, *d_x = nullptr, *d_y = nullptr;
+    int32_t *d_targets = nullptr, *d_argmax = nullptr;
+    float *d_logp = nullptr, *d_loss_n = nullptr, *d_loss = nullptr;
+    int *d_errors = nullptr;
+    // fp32 path (NCHW)
+    std::vector<float *> act;          // act[0] = input planes, act[l] = h_l
+    float *dz[2] = {nullptr, nullptr};
+    // bf16 tcgen05 path
+    Bf16Path *bf = nullptr;
+};
+
+// conv_umma.cu
+int dg_bf16_create(dg_model *m);
+void dg_bf16_destroy(dg_model *m);
+int dg_bf16_params_changed(dg_model *m);                 // refresh bf16 operand copies from the fp32 master
+int dg_bf16_stage_planes(dg_model *m);                   // act[0] (fp32 NCHW) -> blocked bf16 input image
+int dg_bf16_stage_raw(dg_model *m);                      // raw records -> blocked bf16 input image
+int dg_bf16_forward(dg_model *m);                        // fills m->d_logp-ready logits via head
+int dg_bf16_backward(dg_model *m, float scale);

@@ -1,0 +1,175 @@
+"""Thin numpy-facing wrapper over the C ABI (include/deepgo.h).  Every call goes through
+libdeepgo_b200.so; nothing here computes."""
+import numpy as np
+
+import deepgo_b200 as _dg
+from deepgo_b200 import ffi, check, DG_PREC_FP32, DG_PREC_BF16, DG_FMT_F32_NCHW, DG_FMT_BITPLANES  # noqa: F401
+
+
+def _u8(a):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a, ffi.cast("const uint8_t *", a.ctypes.data)
+
+
+def _opt_u8(a):
+    if a is None:
+        return None, ffi.NULL
+    return _u8(a)
+
+
+def device_count():
+    n = ffi.new("int *")
+    check(_dg.lib().dg_device_count(n))
+    return n[0]
+
+
+def encode_labels(x, y, sym=None):
+    """0-based labels of 1-based moves (dataloader.lua:89) under symmetry `sym`."""
+    xa, xp = _u8(x); ya, yp = _u8(y); sa, sp = _opt_u8(sym)
+    out = np.empty(len(xa), np.int32)
+    check(_dg.lib().dg_encode_labels(xp, yp, sp, len(xa), ffi.cast("int32_t *", out.ctypes.data)))
+    return out
+
+
+class Context:
+    def __init__(self, device=0):
+        self.L = _dg.lib()
+        p = ffi.new("dg_ctx **")
+        check(self.L.dg_ctx_create(device, p))
+        self.h = ffi.gc(p[0], self.L.dg_ctx_destroy)
+        self.device = device
+
+    def synchronize(self):
+        check(self.L.dg_ctx_synchronize(self.h))
+
+    def launch_count(self):
+        n = ffi.new("long long *")
+        check(self.L.dg_ctx_launch_count(self.h, n))
+        return int(n[0])
+
+    def timer_start(self):
+        check(self.L.dg_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = ffi.new("float *")
+        check(self.L.dg_timer_stop(self.h, ms))
+        return float(ms[0])
+
+    def flush_l2(self):
+        check(self.L.dg_ctx_flush_l2(self.h))
+
+    def init_dp(self, rank, world, uid):
+        check(self.L.dg_ctx_init_dp(self.h, rank, world, ffi.from_buffer(uid)))
+
+    def encode(self, raw, player, rank, sym=None, fmt=DG_FMT_F32_NCHW):
+        """preprocess() over a batch (dataloader.lua:50-92): -> float32[n,37,19,19] or uint32[n,37,12] bit-planes."""
+        ra, rp = _u8(raw); pa, pp = _u8(player); ka, kp = _u8(rank); sa, sp = _opt_u8(sym)
+        n = len(pa)
+        out = np.empty((n, 37, 19, 19), np.float32) if fmt == DG_FMT_F32_NCHW else np.empty((n, 37, 12), np.uint32)
+        check(self.L.dg_encode(self.h, rp, pp, kp, sp, n, ffi.cast("void *", out.ctypes.data), fmt))
+        return out
+
+    def summarize_boards(self, stones):
+        sa, sp = _u8(stones)
+        n = sa.reshape(-1, 19, 19).shape[0]
+        out = np.empty((n, 7, 19, 19), np.uint8)
+        check(self.L.dg_summarize_boards(self.h, sp, ffi.cast("uint8_t *", out.ctypes.data), n))
+        return out
+
+
+def dp_unique_id():
+    buf = bytearray(128)
+    check(_dg.lib().dg_dp_unique_id(ffi.from_buffer(buf)))
+    return bytes(buf)
+
+
+class Model:
+    """getBasicModel (experiments.lua:133-153) + its flat parameter / gradient vectors (:105-107)."""
+
+    def __init__(self, ctx, num_layers, channel_size, precision=DG_PREC_BF16, max_batch=128, in_planes=37, k_first=5):
+        self.ctx, self.L = ctx, ctx.L
+        p = ffi.new("dg_model **")
+        check(self.L.dg_model_create(ctx.h, num_layers, channel_size, in_planes, k_first, precision, max_batch, p))
+        self.h = ffi.gc(p[0], self.L.dg_model_destroy)
+        n = ffi.new("size_t *")
+        check(self.L.dg_model_param_count(self.h, n))
+        self.P = int(n[0])
+        self.n = 0
+
+    def set_params(self, flat):
+        a = np.ascontiguousarray(flat, dtype=np.float32)
+        check(self.L.dg_model_set_params(self.h, ffi.cast("const float *", a.ctypes.data), a.size))
+
+    def _get(self, fn):
+        out = np.empty(self.P, np.float32)
+        check(fn(self.h, ffi.cast("float *", out.ctypes.data), out.size))
+        return out
+
+    def get_params(self):
+        return self._get(self.L.dg_model_get_params)
+
+    def get_grads(self):
+        return self._get(self.L.dg_model_get_grads)
+
+    def zero_grads(self):
+        check(self.L.dg_zero_grads(self.h))
+
+    def set_global_batch(self, gb):
+        check(self.L.dg_model_set_global_batch(self.h, gb))
+
+    def set_batch_raw(self, raw, player, rank, sym=None, x=None, y=None):
+        ra, rp = _u8(raw); pa, pp = _u8(player); ka, kp = _u8(rank)
+        sa, sp = _opt_u8(sym); xa, xp = _opt_u8(x); ya, yp = _opt_u8(y)
+        self.n = len(pa)
+        check(self.L.dg_model_set_batch_raw(self.h, rp, pp, kp, sp, xp, yp, self.n))
+
+    def set_batch_planes(self, planes, targets0=None):
+        a = np.ascontiguousarray(planes, dtype=np.float32)
+        self.n = a.shape[0]
+        if targets0 is None:
+            tp = ffi.NULL
+        else:
+            t = np.ascontiguousarray(targets0, dtype=np.int32)
+            tp = ffi.cast("const int32_t *", t.ctypes.data)
+        check(self.L.dg_model_set_batch_planes(self.h, ffi.cast("const float *", a.ctypes.data), tp, self.n))
+
+    def forward(self, want_logp=True):
+        if not want_logp:
+            check(self.L.dg_forward(self.h, ffi.NULL))
+            return None
+        out = np.empty((self.n, 361), np.float32)
+        check(self.L.dg_forward(self.h, ffi.cast("float *", out.ctypes.data)))
+        return out
+
+    def loss_backward(self):
+        loss = ffi.new("float *")
+        check(self.L.dg_loss_backward(self.h, loss))
+        return float(loss[0])
+
+    def sgd_step(self, rate):
+        check(self.L.dg_sgd_step(self.h, rate))
+
+    def train_step(self, rate, want_loss=True):
+        if not want_loss:
+            check(self.L.dg_train_step(self.h, rate, ffi.NULL))
+            return None
+        loss = ffi.new("float *")
+        check(self.L.dg_train_step(self.h, rate, loss))
+        return float(loss[0])
+
+    def argmax(self):
+        out = np.empty(self.n, np.int32)
+        check(self.L.dg_argmax(self.h, ffi.cast("int32_t *", out.ctypes.data)))
+        return out
+
+    def eval_batch(self):
+        e = ffi.new("int *"); c = ffi.new("float *")
+        check(self.L.dg_eval_batch(self.h, e, c))
+        return int(e[0]), float(c[0])
+
+    def predict_sym8(self, want_probs=True):
+        probs = np.empty((self.n, 361), np.float32) if want_probs else None
+        am = np.empty(self.n, np.int32)
+        check(self.L.dg_predict_sym8(self.h, ffi.cast("float *", probs.ctypes.data) if want_probs else ffi.NULL,
+                                     ffi.cast("int32_t *", am.ctypes.data)))
+        return probs, am

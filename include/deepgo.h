@@ -1,0 +1,133 @@
+/*
+ * deepgo.h -- C ABI of libdeepgo_b200.so: the B200-native replacement for the hot path of
+ * vipmath/deep-go (Torch7 move-prediction net).  Plain C, no macros in the declared part, so the
+ * same text can be fed to LuaJIT `ffi.cdef` and to Python `cffi`.
+ *
+ * Conventions
+ *   - every function returns int: 0 = ok, non-zero = error; dg_last_error() gives the text
+ *     (thread-local).  No C++ exception or longjmp crosses this boundary, so the reference's
+ *     pcall() guard (train.lua:106) keeps working through the Lua shim.
+ *   - indices are 0-based on this side (labels, argmax, board x/y); the Lua shim adds/subtracts 1
+ *     (dataloader.lua:89, train.lua:29-36 are 1-based).
+ *   - caller owns every host buffer; the library owns all device memory.  Handles are opaque.
+ *   - one caller thread per dg_ctx.  GPU work is asynchronous on the context's stream; a call
+ *     synchronises only when it returns a scalar or fills a host buffer.
+ *   - there is NO CPU fallback: every compute entry point fails with an error if no B200 is present.
+ *
+ * References are to files of the reference repository (file:line).
+ */
+#ifndef DEEPGO_H
+#define DEEPGO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct dg_ctx dg_ctx;
+typedef struct dg_model dg_model;
+
+/* precision of the conv stack */
+enum { DG_PREC_FP32 = 0, DG_PREC_BF16 = 1 };
+/* output formats of dg_encode */
+enum { DG_FMT_F32_NCHW = 0, DG_FMT_BITPLANES = 1 };
+
+/* ---- errors / info ----------------------------------------------------------------------- */
+/* replaces Lua error() text seen by pcall (train.lua:106-109) */
+const char *dg_last_error(void);
+int dg_version(void);
+/* number of visible CUDA devices (cutorch.getDeviceCount, experiments.lua:157) */
+int dg_device_count(int *out);
+
+/* ---- context: one device, one stream (cutorch.setDevice, default-experiment.lua:6) --------- */
+int dg_ctx_create(int device, dg_ctx **out);
+int dg_ctx_destroy(dg_ctx *ctx);
+int dg_ctx_synchronize(dg_ctx *ctx);
+/* kernels this library has launched on ctx so far (bench.py "gpu_launches") */
+int dg_ctx_launch_count(dg_ctx *ctx, long long *out);
+/* CUDA-event timer on the context's stream (sys.clock() pairs, train.lua:91,94,113,137) */
+int dg_timer_start(dg_ctx *ctx);
+int dg_timer_stop(dg_ctx *ctx, float *ms_out);
+/* write `bytes` of device memory (L2 flush between timed iterations) */
+int dg_ctx_flush_l2(dg_ctx *ctx);
+
+/* ---- data parallel (nn.DataParallelTable(1), experiments.lua:155-168) ---------------------- */
+/* One process per GPU.  Rank 0 calls dg_dp_unique_id and ships the 128 bytes to the other ranks
+ * (any side channel); every rank then calls dg_ctx_init_dp.  After that dg_train_step* sums the
+ * gradient over ranks (NCCL allreduce, per-layer buckets) before the SGD update; each rank must
+ * scale its loss gradient by 1/global_batch (dg_model_set_global_batch) so the sum is the
+ * global-batch mean gradient -- what DataParallelTable + ClassNLLCriterion on the gathered output
+ * produce. */
+int dg_dp_unique_id(char id_out[128]);
+int dg_ctx_init_dp(dg_ctx *ctx, int rank, int world, const char id[128]);
+
+/* ---- feature planes (dataloader.lua) ------------------------------------------------------ */
+/* preprocess() over a batch (dataloader.lua:50-92,113-121) with the D4 symmetry hook
+ * (transform(), dataloader.lua:41-44; sym 0 = reference behaviour).
+ *   raw    u8[n][9][19][19]  flatten_data() planes (dataloader.lua:30-39)
+ *   player u8[n] in {1,2}    data.move.player
+ *   rank   u8[n] in 1..9     data.ranks[player]
+ *   sym    u8[n] in 0..7 or NULL (all 0)
+ *   out    DG_FMT_F32_NCHW:  float[n][37][19][19]
+ *          DG_FMT_BITPLANES: uint32[n][37][12]  (bit p%32 of word p/32 = plane value at p=19*x+y)
+ * Host buffers in and out. */
+int dg_encode(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
+              const uint8_t *sym, int n, void *out, int outfmt);
+/* label = 19*(x-1)+y of the transformed move (dataloader.lua:89); x,y 1-based as stored in the
+ * records, result 0-based.  Pure host helper, reentrant. */
+int dg_encode_labels(const uint8_t *x, const uint8_t *y, const uint8_t *sym, int n, int32_t *out);
+
+/* ---- board analysis (makedata.lua) --------------------------------------------------------- */
+/* summarize_board (makedata.lua:143-153): stones u8[n][19][19] in {0,1,2} ->
+ * out u8[n][7][19][19]: liberties, liberties_after[p=1,2], kills[p=1,2], ladders[p=1,2]. */
+int dg_summarize_boards(dg_ctx *ctx, const uint8_t *stones, uint8_t *out, int n);
+
+/* ---- model (experiments.lua:133-153 getBasicModel + :105-107 getParameters) ---------------- */
+/* numLayers x [pad, conv k, +b[c], +a[c,x,y], ReLU] + log-softmax(361); kernels {kFirst,3,3,..},
+ * channels {inPlanes, C,..,C, 1} (experiments.lua:88-93).  max_batch sizes the device buffers. */
+int dg_model_create(dg_ctx *ctx, int num_layers, int channel_size, int in_planes, int k_first,
+                    int precision, int max_batch, dg_model **out);
+int dg_model_destroy(dg_model *m);
+int dg_model_param_count(dg_model *m, size_t *out);
+/* flat parameter / gradient vectors in Torch7 getParameters order: per layer W[cout][cin][k][k],
+ * b[cout], a[cout][19][19] (experiments.lua:105-107) */
+int dg_model_set_params(dg_model *m, const float *host, size_t n);
+int dg_model_get_params(dg_model *m, float *host, size_t n);
+int dg_model_get_grads(dg_model *m, float *host, size_t n);
+/* grads:zero() (train.lua:5) */
+int dg_zero_grads(dg_model *m);
+/* loss-gradient scale 1/global_batch for data-parallel shards; 0 = use the local batch size */
+int dg_model_set_global_batch(dg_model *m, int global_batch);
+
+/* batch staging (cudaInput:resize():copy(), train.lua:98-104)
+ *   _raw:    records + on-device encode; x,y 1-based move (label computed on device)
+ *   _planes: the reference's own staging: float[n][37][19][19] planes + 0-based targets */
+int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
+                           const uint8_t *sym, const uint8_t *x, const uint8_t *y, int n);
+int dg_model_set_batch_planes(dg_model *m, const float *planes, const int32_t *targets0, int n);
+
+/* model:forward (train.lua:6,28): log-probs float[n][361] to host if logprobs_out != NULL */
+int dg_forward(dg_model *m, float *logprobs_out);
+/* criterion:forward + criterion:backward + model:backward (train.lua:8-10); needs dg_forward first.
+ * Accumulates into the gradient vector (call dg_zero_grads first, as eval() does). */
+int dg_loss_backward(dg_model *m, float *loss_out);
+/* SGD:step (optimizer.lua:24-25): p += -rate*g.  The rate decay (:26) stays on the host side. */
+int dg_sgd_step(dg_model *m, float rate);
+/* eval() + optimizer:step fused (train.lua:111,131): zero grads, forward, NLL, backward,
+ * [allreduce], SGD.  loss_out may be NULL (no host sync). */
+int dg_train_step(dg_model *m, float rate, float *loss_out);
+/* preds:max(2) (train.lua:29): 0-based argmax of the last forward, int32[n] to host */
+int dg_argmax(dg_model *m, int32_t *out);
+/* eval_validation inner loop (train.lua:28-37): forward + top-1 errors + mean NLL of the staged batch */
+int dg_eval_batch(dg_model *m, int *errors_out, float *cost_out);
+
+/* c5 inference: 8-fold symmetry-averaged move probabilities for n records (already staged with
+ * dg_model_set_batch_raw, sym ignored): probs float[n][361] (may be NULL), argmax int32[n] (may be NULL) */
+int dg_predict_sym8(dg_model *m, float *probs_out, int32_t *argmax_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEEPGO_H */
