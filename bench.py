@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""bench.py -- training positions/sec (fwd+bwd+SGD) of the deep-go policy net on N B200s.
+
+Workload (BASELINE.json configs[1]): 12 conv layers x 128 filters (5x5 first, 3x3 rest, 361-way softmax),
+batch 128 per GPU, synthetic positions drawn (seeded) from the fixture corpus, He-scaled random weights.
+A step = on-device feature-plane encode of the resident records + zero grads + forward + NLL + backward
++ [gradient allreduce] + SGD update + bf16 operand repack.  One JSON line on stdout (rank 0).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+N > 1: launched by torch.distributed.run, one process per GPU (weak scaling: 128 positions per GPU).
+--impl reference: the reference's CPU path (oracle restatement of the Torch7 nn path; Torch7 itself cannot run
+on this image) timed on the host cores, same metric and config.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+L, C, BATCH = 12, 128, 128
+METRIC = "training positions/sec (fwd+bwd+SGD)"
+UNIT = "positions/s"
+F_TRAIN = 3.3674e9          # algorithmic FLOPs / position, SURVEY.md 8(d): 3*F_fwd - F_fwd(layer 1)
+F_CONV_LAYER = 2 * 361 * 9 * C * C          # one 3x3 C->C layer, per position (106.5 MFLOP)
+
+
+def config(n_gpus):
+    return {"workload": "c2: policy net 12 layers x 128 filters (5x5 first, 3x3 rest), batch 128/GPU, 19x19x37 planes",
+            "num_layers": L, "channel_size": C, "batch_per_gpu": BATCH, "global_batch": BATCH * n_gpus,
+            "parallelism": "dp%d" % n_gpus, "precision": "bf16 operands, fp32 accumulate, fp32 master weights",
+            "l2": "256 MB device fill between timed steps (untimed); per-step CUDA events on the library stream",
+            "optimizer": "SGD, momentum 0 (optimizer.lua:24-27)"}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops_sustained", d["bf16_tflops"]), d["bf16_tflops"], d["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
+    return 1400.0, 1590.0, 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def synthetic_batch(seed, n):
+    g = np.load(os.path.join(ROOT, "tests", "golden", "positions.npz"))
+    rng = np.random.default_rng(seed)
+    idx = rng.integers(0, len(g["raw"]), n)
+    pl = g["player"][idx]
+    return dict(raw=np.ascontiguousarray(g["raw"][idx]), player=pl, rank=g["ranks"][idx, pl - 1],
+                sym=rng.integers(0, 8, n).astype(np.uint8), x=g["x"][idx], y=g["y"][idx])
+
+
+def he_params(seed):
+    """He-scaled N(0, 2/fan_in) weights of the c2 architecture in Torch7 flat order (W1 of SURVEY.md 8(d))."""
+    rng = np.random.default_rng(seed)
+    chans = [37] + [C] * (L - 1) + [1]
+    ks = [5] + [3] * (L - 1)
+    parts = []
+    for i in range(L):
+        fan = chans[i] * ks[i] * ks[i]
+        parts.append(rng.normal(0, np.sqrt(2.0 / fan), chans[i + 1] * fan))
+        parts.append(rng.normal(0, 0.05, chans[i + 1]))
+        parts.append(rng.normal(0, 0.05, chans[i + 1] * 361))
+    return np.concatenate(parts).astype(np.float32)
+
+
+class ClockSampler:
+    FIELDS = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out, _ = self.p.communicate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [t.strip() for t in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+def cpu_step_fn(batch, threads):
+    """One fwd+bwd+SGD step of the oracle restatement (fp64 = Torch7's CPU tensor type), one eval per step
+    (the reference's duplicate pcall eval, train.lua:106, is not replicated)."""
+    import torch
+    from oracle import encode, net
+    torch.set_num_threads(threads)
+    b = synthetic_batch(1, batch)
+    x, t = encode.load_minibatch(b["raw"], b["player"], b["rank"], b["x"], b["y"], b["sym"])
+    x = torch.from_numpy(x)
+    flat = torch.from_numpy(he_params(2)).double()
+
+    def step():
+        _, g, _ = net.loss_and_grads(flat, x, t, L, C)
+        net.sgd_step(flat, g, 0.01, 1e-7)
+    return step
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    # bounded sample: batch sized so that the whole run ends within ~2 minutes
+    probe = cpu_step_fn(4, threads)
+    probe()
+    t0 = time.perf_counter(); probe(); t4 = time.perf_counter() - t0
+    budget = 100.0 / max(1, args.steps + args.warmup)
+    sb = int(max(2, min(BATCH, 4 * budget / max(t4, 1e-3))))
+    step = cpu_step_fn(sb, threads)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    v = sb * args.steps / dt
+    sample = "%d steps of %d positions (of the %d-position batch), fp64 torch-CPU restatement of the Torch7 nn path" % (args.steps, sb, BATCH)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": config(args.gpus),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ------------------------------------------------------------------------------------------------------------
+def run_ours(args, rank, local_rank, world):
+    import torch
+    import __graft_entry__ as entry
+    if not os.path.exists(os.path.join(ROOT, "deep-go_b200", "libdeepgo_b200.so")):
+        entry.build()
+    from deepgo_b200.host import engine
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    ctx = engine.Context(local_rank)
+    if world > 1:
+        obj = [engine.dp_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        ctx.init_dp(rank, world, obj[0])
+    m = engine.Model(ctx, L, C, engine.DG_PREC_BF16, max_batch=BATCH)
+    m.set_params(he_params(2))
+    m.set_global_batch(BATCH * world)
+    b = synthetic_batch(100 + rank, BATCH)
+    rate = 0.01
+
+    def barrier():
+        ctx.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---------------- device-resident throughput ("value") ----------------
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    for _ in range(max(3, args.warmup)):
+        m.encode_resident(); m.train_step(rate, want_loss=False)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = ctx.launch_count()
+    total_ms, launches = 0.0, 0
+    for _ in range(args.steps):
+        ctx.flush_l2()
+        lc = ctx.launch_count()
+        ctx.timer_start()
+        m.encode_resident(); m.train_step(rate, want_loss=False)
+        total_ms += ctx.timer_stop()
+        launches += ctx.launch_count() - lc
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    if dist is not None:
+        t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    value = BATCH * world / (ms_per_step * 1e-3)
+
+    # ---------------- end to end through the C ABI with host buffers ----------------
+    pin = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy() for k, v in b.items()}
+    for _ in range(3):
+        m.set_batch_raw(pin["raw"], pin["player"], pin["rank"], pin["sym"], pin["x"], pin["y"]); m.train_step(rate)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        m.set_batch_raw(pin["raw"], pin["player"], pin["rank"], pin["sym"], pin["x"], pin["y"])
+        loss = m.train_step(rate)          # returns the step's loss: D2H read + sync inside
+    ctx.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = BATCH * world * args.steps / e2e_s
+    h2d = BATCH * (9 * 361 + 5)
+    assert np.isfinite(loss)
+
+    if rank != 0:
+        return
+    # ---------------- per-kernel times for the roofline (a few extra steps, after the timed region) ----------------
+    ctx.prof_begin()
+    for _ in range(5):
+        m.encode_resident(); m.train_step(rate, want_loss=False)
+    prof = ctx.prof_end()
+    sustained, burst, hbm, peak_src = peaks()
+    kern = {k: {"ms_per_step": v[0] / 5, "launches_per_step": v[1] / 5} for k, v in prof.items()}
+    conv_ms, conv_n = prof.get("conv", (0.0, 0))
+    roofline = None
+    if conv_n:
+        avg_ms = conv_ms / conv_n
+        achieved = F_CONV_LAYER * BATCH / (avg_ms * 1e-3) / 1e12
+        roofline = {"kernel": "conv_umma_kernel (3x3, 128->128, forward)", "bound": "tensor", "achieved": achieved, "peak": sustained,
+                    "unit": "TFLOP/s", "frac": achieved / sustained, "traffic": None, "peak_source": peak_src + ", sustained bf16",
+                    "avg_launch_ms": avg_ms, "flops_per_launch": F_CONV_LAYER * BATCH}
+    whole = F_TRAIN * BATCH / (ms_per_step * 1e-3) / 1e12
+
+    # ---------------- CPU baseline: oracle port on the host cores, bounded sample ----------------
+    threads = os.cpu_count() or 1
+    sb = 16
+    step = cpu_step_fn(sb, threads)
+    step()
+    t0 = time.perf_counter(); n_cpu = 0
+    while time.perf_counter() - t0 < 12.0 and n_cpu < 8:
+        step(); n_cpu += 1
+    cpu_dt = time.perf_counter() - t0
+    cpu = {"value": sb * n_cpu / cpu_dt, "unit": UNIT, "cores": threads, "kind": "port",
+           "sample": "%d steps of %d positions, fp64 torch-CPU restatement of the Torch7 nn path (Torch7 not runnable here)" % (n_cpu, sb)}
+
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic", "config": config(world), "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+        "tensor_frac_whole_step": {"achieved_tflops": whole, "of_sustained_peak": whole / sustained, "of_burst_peak": whole / burst},
+        "kernels": kern}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -83,6 +83,31 @@ extern "C" int dg_timer_stop(dg_ctx *c, float *ms) {
     return 0;
 }
 
+extern "C" int dg_prof_begin(dg_ctx *c) {
+    DG_REQUIRE(c, "dg_prof_begin: ctx is NULL");
+    for (int k = 0; k < DG_K_COUNT; ++k) { c->prof_ms[k] = 0; c->prof_n[k] = 0; }
+    c->prof_on = true;
+    return 0;
+}
+extern "C" int dg_prof_end(dg_ctx *c) {
+    DG_REQUIRE(c, "dg_prof_end: ctx is NULL");
+    c->prof_on = false;
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    for (dg_prof_rec &r : c->prof_recs) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) { c->prof_ms[r.kind] += ms; c->prof_n[r.kind]++; }
+        cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+    }
+    c->prof_recs.clear();
+    return 0;
+}
+extern "C" int dg_prof_get(dg_ctx *c, int kind, float *ms_total, long long *launches) {
+    DG_REQUIRE(c && kind >= 0 && kind < DG_K_COUNT, "dg_prof_get: bad argument");
+    if (ms_total) *ms_total = (float)c->prof_ms[kind];
+    if (launches) *launches = c->prof_n[kind];
+    return 0;
+}
+
 extern "C" int dg_ctx_flush_l2(dg_ctx *c) {
     DG_REQUIRE(c, "dg_ctx_flush_l2: ctx is NULL");
     DG_CUDA(cudaSetDevice(c->dev));
@@ -299,6 +324,17 @@ extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uin
         if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
     }
     if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]);
+    return dg_bf16_stage_raw(m);
+}
+
+extern "C" int dg_model_encode_resident(dg_model *m) {
+    DG_REQUIRE(m, "dg_model_encode_resident: model is NULL");
+    DG_REQUIRE(m->have_raw && m->n > 0, "dg_model_encode_resident: no raw records staged (dg_model_set_batch_raw)");
+    dg_ctx *c = m->ctx;
+    DG_CUDA(cudaSetDevice(c->dev));
+    m->forward_done = false;
+    if (m->have_targets) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, m->n, m->d_targets)) return rc;
+    if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, m->n, m->act[0]);
     return dg_bf16_stage_raw(m);
 }
 

@@ -31,8 +31,19 @@ void dg_set_error(const char *fmt, ...);
         }                                                                                          \
     } while (0)
 
+enum {
+    DG_K_ENCODE = 0, DG_K_CONV_FIRST, DG_K_CONV, DG_K_DGRAD, DG_K_WGRAD, DG_K_WGRAD_REDUCE, DG_K_BIAS_GRAD,
+    DG_K_HEAD, DG_K_SGD, DG_K_PACK, DG_K_ALLREDUCE, DG_K_OTHER, DG_K_COUNT
+};
+
+struct dg_prof_rec { int kind; cudaEvent_t e0, e1; };
+
 struct dg_ctx {
     int dev = 0;
+    bool prof_on = false;
+    std::vector<dg_prof_rec> prof_recs;
+    double prof_ms[DG_K_COUNT] = {0};
+    long long prof_n[DG_K_COUNT] = {0};
     cudaStream_t stream = nullptr;
     long long launches = 0;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
@@ -56,6 +67,20 @@ struct LayerInfo {
 };
 
 int dg_ctx_scratch(dg_ctx *ctx, size_t bytes, void **out);
+
+// per-kernel CUDA-event timing (dg_prof_*): brackets one launch on the context's stream when enabled
+struct dg_prof_scope {
+    dg_ctx *c; int idx;
+    dg_prof_scope(dg_ctx *ctx, int kind) : c(ctx), idx(-1) {
+        if (!c->prof_on) return;
+        dg_prof_rec r; r.kind = kind;
+        cudaEventCreate(&r.e0); cudaEventCreate(&r.e1);
+        cudaEventRecord(r.e0, c->stream);
+        c->prof_recs.push_back(r);
+        idx = (int)c->prof_recs.size() - 1;
+    }
+    ~dg_prof_scope() { if (idx >= 0) cudaEventRecord(c->prof_recs[idx].e1, c->stream); }
+};
 
 // ---- encode.cu
 int dg_launch_encode_f32(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,

@@ -70,8 +70,8 @@ int dg_simt_conv(dg_ctx *ctx, const float *in, const float *W, const float *b, c
     if (n <= 0) return 0;
     constexpr int CO_T = 8, CI_T = 8;
     dim3 grid(n, (cout + CO_T - 1) / CO_T);
-    if (k == 3) conv_simt_kernel<3, CO_T, CI_T><<<grid, 384, 0, ctx->stream>>>(in, W, b, a, mask, out, cin, cout, transposed, relu);
-    else if (k == 5) conv_simt_kernel<5, CO_T, CI_T><<<grid, 384, 0, ctx->stream>>>(in, W, b, a, mask, out, cin, cout, transposed, relu);
+    if (k == 3) { dg_prof_scope _ps(ctx, transposed ? DG_K_DGRAD : DG_K_CONV); conv_simt_kernel<3, CO_T, CI_T><<<grid, 384, 0, ctx->stream>>>(in, W, b, a, mask, out, cin, cout, transposed, relu); }
+    else if (k == 5) { dg_prof_scope _ps(ctx, transposed ? DG_K_DGRAD : DG_K_CONV_FIRST); conv_simt_kernel<5, CO_T, CI_T><<<grid, 384, 0, ctx->stream>>>(in, W, b, a, mask, out, cin, cout, transposed, relu); }
     else DG_REQUIRE(false, "conv kernel size %d not supported (3 or 5)", k);
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
@@ -135,10 +135,14 @@ int dg_simt_wgrad(dg_ctx *ctx, const float *x, const float *dz, float *gW, int n
     if (n <= 0) return 0;
     if (k == 3) {
         constexpr int CI_T = 4;
+        { dg_prof_scope _ps(ctx, DG_K_WGRAD);
         wgrad_simt_kernel<3, CI_T><<<dim3(cout, (cin + CI_T - 1) / CI_T), 256, 0, ctx->stream>>>(x, dz, gW, n, cin, cout);
+        }
     } else if (k == 5) {
         constexpr int CI_T = 2;
+        { dg_prof_scope _ps(ctx, DG_K_WGRAD);
         wgrad_simt_kernel<5, CI_T><<<dim3(cout, (cin + CI_T - 1) / CI_T), 256, 0, ctx->stream>>>(x, dz, gW, n, cin, cout);
+        }
     } else DG_REQUIRE(false, "conv kernel size %d not supported (3 or 5)", k);
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
@@ -168,7 +172,9 @@ __global__ void __launch_bounds__(384) bias_grad_simt_kernel(const float *__rest
 
 int dg_simt_bias_grad(dg_ctx *ctx, const float *dz, float *ga, float *gb, int n, int cout) {
     if (n <= 0) return 0;
+    { dg_prof_scope _ps(ctx, DG_K_BIAS_GRAD);
     bias_grad_simt_kernel<<<cout, 384, 0, ctx->stream>>>(dz, ga, gb, n, cout);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;

@@ -1,9 +1,938 @@
-// placeholder until the tcgen05 path lands
+// DG_PREC_BF16 path: the conv stack of experiments.lua:133-153 as implicit-GEMM tcgen05 kernels.
+//
+// Activation layout in HBM ("blocked image"): per position  [C/8][R][8] bf16, R rows of 8 channels
+// (16 B).  Row index rho = x'*pitch + y' over a zero-padded board whose right pad column(s) double
+// as the next board row's left pad (pitch = 19 + pad): a k x k tap (ky,kx) is then the SAME image
+// read at row offset (ky-pad)*pitch + (kx-pad).  With the no-swizzle UMMA canonical layout
+// (8 rows x 16 B core matrices) that is just a different descriptor start address, so one
+// bulk-copied image in shared memory feeds all k*k taps: no im2col, no re-fetch per tap.
+//   forward / input-gradient:  D[rho][co] += A(image rows, K-major) x B(weights [ci/8][co][8], K-major)
+//   weight-gradient:           D[co][ci]  += A(dZ image, MN-major)  x B(X image shifted, MN-major)
+// Accumulators live in TMEM; the epilogue fuses bias + per-point bias + ReLU (forward) or the
+// ReLU mask (backward) and writes bf16 back in the same blocked layout.
 #include "model.cuh"
-int dg_bf16_create(dg_model *m) { dg_set_error("DG_PREC_BF16 path not built yet"); return 3; }
-void dg_bf16_destroy(dg_model *m) {}
-int dg_bf16_params_changed(dg_model *m) { return 0; }
-int dg_bf16_stage_planes(dg_model *m) { return 3; }
-int dg_bf16_stage_raw(dg_model *m) { return 3; }
-int dg_bf16_forward(dg_model *m) { return 3; }
-int dg_bf16_backward(dg_model *m, float scale) { return 3; }
+#include "umma.cuh"
+#include "../../include/deepgo.h"
+
+using namespace umma;
+typedef __nv_bfloat16 bf16;
+
+#define DG_R3 432      // image rows, 3x3 geometry: pitch 20, pad 1 (rows 0..420 used, MMA tiles read up to 425)
+#define DG_R5 600      // image rows, 5x5 geometry: pitch 21, pad 2 (rows 0..484 used, MMA tiles read up to 599)
+
+struct Geom { int pitch, pad, rows, first, ntiles; };
+static Geom geom_for(int k) {
+    Geom g;
+    g.pad = k / 2; g.pitch = DG_BOARD + g.pad; g.rows = k == 5 ? DG_R5 : DG_R3;
+    g.first = g.pad * g.pitch + g.pad;
+    g.ntiles = k == 5 ? 4 : 3;
+    return g;
+}
+
+// ---------------------------------------------------------------------------------------------
+// conv forward / input gradient
+// ---------------------------------------------------------------------------------------------
+struct ConvParams {
+    const bf16 *in;       // [n][cin/8][R_in][8]
+    const bf16 *w;        // [taps][cin/8][cout][8]
+    bf16 *out;            // [n][cout/8][R_out][8]
+    const float *bias;    // mode 0: [cout/8][R_out][8] fp32, b[c] + a[c][x][y]
+    const bf16 *mask;     // mode 1: [n][cout/8][R_mask][8], output kept where mask > 0
+    int n, cin, cout;
+    int R_in, pitch_in, pad_in, ksize, first, ntiles;
+    int R_out, pitch_out, pad_out;
+    int R_mask, pitch_mask, pad_mask;
+    int nb;               // N block (<= 256, multiple of 16); cout % nb == 0
+    int kp;               // channels per weight ring stage (multiple of 16); cin % kp == 0
+    int nstages;
+    int mode;
+};
+
+#define CONV_MAX_STAGES 8
+#define CONV_MAX_KPANELS 4
+
+__global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES];
+    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_empty, acc_full, acc_empty;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int chunks_in = p.cin >> 3;
+    const uint32_t img_bytes = (uint32_t)chunks_in * p.R_in * 16;
+    const uint32_t stage_bytes = (uint32_t)p.kp * p.nb * 2;
+    uint8_t *img = smem;
+    uint8_t *ring = smem + ((img_bytes + 1023) & ~1023u);
+    const int taps = p.ksize * p.ksize;
+    const int nkp = p.cin / p.kp;
+    const int nnb = p.cout / p.nb;
+    const int chunks_kp = p.kp >> 3;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+        for (int k = 0; k < nkp; ++k) mbar_init(&img_full[k], 1);
+        mbar_init(&img_empty, 1);
+        mbar_init(&acc_full, 1);
+        mbar_init(&acc_empty, 4);
+        fence_barrier_init();
+    }
+    if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        // ===== producer: bulk copies of the position image and of the weight ring =====
+        if (lane == 0) {
+            uint32_t it = 0, j = 0;
+            for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
+                mbar_wait(&img_empty, (j & 1) ^ 1);
+                const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
+                for (int k = 0; k < nkp; ++k) {
+                    mbar_arrive_expect_tx(&img_full[k], (uint32_t)chunks_kp * p.R_in * 16);
+                    for (int c = 0; c < chunks_kp; ++c) {
+                        const size_t off = (size_t)(k * chunks_kp + c) * p.R_in * 16;
+                        bulk_g2s(img + off, src + off, (uint32_t)p.R_in * 16, &img_full[k]);
+                    }
+                }
+                for (int nbk = 0; nbk < nnb; ++nbk)
+                    for (int k = 0; k < nkp; ++k)
+                        for (int t = 0; t < taps; ++t, ++it) {
+                            const int s = it % p.nstages;
+                            mbar_wait(&w_empty[s], ((it / p.nstages) & 1) ^ 1);
+                            mbar_arrive_expect_tx(&w_full[s], stage_bytes);
+                            uint8_t *dst = ring + (size_t)s * stage_bytes;
+                            // W[t][k*chunks_kp + c][nbk*nb .. +nb][8]
+                            const uint8_t *wsrc = (const uint8_t *)p.w + (((size_t)t * chunks_in + (size_t)k * chunks_kp) * p.cout + (size_t)nbk * p.nb) * 16;
+                            if (nnb == 1) {
+                                bulk_g2s(dst, wsrc, stage_bytes, &w_full[s]);
+                            } else {
+                                for (int c = 0; c < chunks_kp; ++c)
+                                    bulk_g2s(dst + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
+                            }
+                        }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(128, p.nb, 0, 0);
+            const uint32_t img_a = smem_u32(img), ring_a = smem_u32(ring);
+            uint32_t it = 0, j = 0, a = 0;
+            for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
+                for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
+                    mbar_wait(&acc_empty, (a & 1) ^ 1);
+                    tc_fence_after();
+                    for (int k = 0; k < nkp; ++k) {
+                        if (nbk == 0) mbar_wait(&img_full[k], j & 1);
+                        for (int t = 0; t < taps; ++t, ++it) {
+                            const int s = it % p.nstages;
+                            mbar_wait(&w_full[s], (it / p.nstages) & 1);
+                            tc_fence_after();
+                            const int ky = t / p.ksize, kx = t - ky * p.ksize;
+                            const int toff = (ky - p.pad_in) * p.pitch_in + (kx - p.pad_in);
+                            const uint32_t b_base = ring_a + s * stage_bytes;
+                            for (int tile = 0; tile < p.ntiles; ++tile) {
+                                const uint32_t a_row = (uint32_t)(p.first + tile * 128 + toff);
+                                for (int ks = 0; ks < (p.kp >> 4); ++ks) {
+                                    const uint32_t a_addr = img_a + ((uint32_t)(k * chunks_kp + ks * 2) * p.R_in + a_row) * 16;
+                                    const uint64_t ad = make_desc(a_addr, (uint32_t)p.R_in * 16, 128);
+                                    const uint64_t bd = make_desc(b_base + (uint32_t)(ks * 2) * p.nb * 16, (uint32_t)p.nb * 16, 128);
+                                    mma_bf16(tmem_base + tile * p.nb, ad, bd, idesc, (k | t | ks) != 0);
+                                }
+                            }
+                            mma_commit(&w_empty[s]);
+                        }
+                    }
+                    mma_commit(&acc_full);
+                }
+                mma_commit(&img_empty);
+            }
+        }
+    } else {
+        // ===== epilogue warps 2..5: TMEM -> registers -> bias/ReLU or mask -> bf16 -> HBM =====
+        const int q = warp & 3;                         // TMEM lane quarter this warp may access
+        const int chunks_out = p.cout >> 3;
+        uint32_t a = 0;
+        for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x) {
+            for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
+                mbar_wait(&acc_full, a & 1);
+                tc_fence_after();
+                for (int tile = 0; tile < p.ntiles; ++tile) {
+                    const int rho = p.first + tile * 128 + q * 32 + lane;
+                    const int xp = rho / p.pitch_in, yp = rho - xp * p.pitch_in;
+                    const int x = xp - p.pad_in, y = yp - p.pad_in;
+                    const bool valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+                    const int rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
+                    for (int c0 = 0; c0 < p.nb; c0 += 32) {
+                        uint32_t r[32];
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+                        tmem_ld_wait();
+                        if (valid) {
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                const int chunk = (nbk * p.nb + c0) / 8 + g;
+                                float v[8];
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
+                                if (p.mode == 0) {
+                                    const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)chunk * p.R_out + rho_out) * 8);
+                                    const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1);
+                                    v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f);
+                                    v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
+                                    v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f);
+                                    v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
+                                } else {
+                                    const int rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
+                                    const uint4 mk = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk) * p.R_mask + rho_m) * 8));
+                                    const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e) {
+                                        const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                                        // bf16 > 0  <=>  sign bit clear and not zero
+                                        if (!(h != 0 && (h & 0x8000u) == 0)) v[e] = 0.f;
+                                    }
+                                }
+                                uint4 o;
+                                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+                                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
+                                o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
+                                o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
+                                *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk) * p.R_out + rho_out) * 8) = o;
+                            }
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight gradient: D[co][ci] per tap, split-K over (position, 64-row panel) units, partial tiles to
+// scratch, then a deterministic reduction into the Torch7-order gradient vector.
+// ---------------------------------------------------------------------------------------------
+struct WgradParams {
+    const bf16 *dz;       // [n][cout/8][R][8]   (A, MN-major: M = cout channel)
+    const bf16 *x;        // [n][cin/8][R][8]    (B, MN-major: N = cin channel)
+    float *scratch;       // [combo][split][k taps][128][nb]
+    int n, cin, cout;     // cin padded (multiple of 16)
+    int R, pitch, pad, ksize, first, ntiles;
+    int nb;               // N block (cin % nb == 0), k*nb <= 512
+    int n_mblk, n_nblk;   // cout / 128 (rounded up), cin / nb
+    int splits;           // split-K CTAs per combo
+    int nstages;
+};
+
+#define WG_RP 64          // K rows per stage
+
+__global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int combo = blockIdx.x / p.splits, split = blockIdx.x - combo * p.splits;
+    // combo -> (ky, mblk, nblk)
+    const int nblk = combo % p.n_nblk, mblk = (combo / p.n_nblk) % p.n_mblk, ky = combo / (p.n_nblk * p.n_mblk);
+    const int rb = WG_RP + 2 * p.pad;                         // B panel rows incl. the kx halo
+    const int rb_pad = (rb + 7) & ~7;
+    const uint32_t a_bytes = 16u * WG_RP * 16;                // 16 channel chunks (M = 128) x 64 rows
+    const uint32_t b_bytes = (uint32_t)(p.nb >> 3) * rb_pad * 16;
+    const uint32_t stage_bytes = a_bytes + b_bytes;
+    const int panels = p.ntiles * 128 / WG_RP;
+    const int units = p.n * panels;
+    const int chunks_dz = p.cout >> 3, chunks_x = p.cin >> 3;
+    // channel chunks of dZ this M block really has (the rest of the 128 lanes accumulate garbage that is never stored)
+    const int a_chunks = min(16, chunks_dz - mblk * 16);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); }
+        mbar_init(&acc_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int u = split; u < units; u += p.splits, ++it) {
+                const int pos = u / panels, panel = u - pos * panels;
+                const int s = it % p.nstages;
+                mbar_wait(&s_empty[s], ((it / p.nstages) & 1) ^ 1);
+                mbar_arrive_expect_tx(&s_full[s], (uint32_t)a_chunks * WG_RP * 16 + (uint32_t)(p.nb >> 3) * rb * 16);
+                uint8_t *sa = smem + (size_t)s * stage_bytes, *sb = sa + a_bytes;
+                const int row0 = p.first + panel * WG_RP;
+                for (int c = 0; c < a_chunks; ++c)
+                    bulk_g2s(sa + (size_t)c * WG_RP * 16, (const uint8_t *)p.dz + (((size_t)pos * chunks_dz + mblk * 16 + c) * p.R + row0) * 16,
+                             WG_RP * 16, &s_full[s]);
+                const int brow0 = row0 + (ky - p.pad) * p.pitch - p.pad;
+                for (int c = 0; c < (p.nb >> 3); ++c)
+                    bulk_g2s(sb + (size_t)c * rb_pad * 16, (const uint8_t *)p.x + (((size_t)pos * chunks_x + nblk * (p.nb >> 3) + c) * p.R + brow0) * 16,
+                             (uint32_t)rb * 16, &s_full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(128, p.nb, 1, 1);
+            uint32_t it = 0;
+            for (int u = split; u < units; u += p.splits, ++it) {
+                const int s = it % p.nstages;
+                mbar_wait(&s_full[s], (it / p.nstages) & 1);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem) + s * stage_bytes, sb = sa + a_bytes;
+                for (int kx = 0; kx < p.ksize; ++kx)
+                    for (int ks = 0; ks < WG_RP / 16; ++ks) {
+                        const uint64_t ad = make_desc(sa + ks * 256, 128, WG_RP * 16);
+                        const uint64_t bd = make_desc(sb + (kx + ks * 16) * 16, 128, (uint32_t)rb_pad * 16);
+                        mma_bf16(tmem_base + kx * p.nb, ad, bd, idesc, (it | ks) != 0);
+                    }
+                mma_commit(&s_empty[s]);
+            }
+            mma_commit(&acc_full);
+        }
+    } else {
+        const int q = warp & 3;
+        mbar_wait(&acc_full, 0);
+        tc_fence_after();
+        const bool any = split < units;                       // a CTA without units holds an unwritten accumulator
+        float *dst = p.scratch + (((size_t)combo * p.splits + split) * p.ksize * 128 + (q * 32 + lane)) * p.nb;
+        for (int kx = 0; kx < p.ksize; ++kx)
+            for (int c0 = 0; c0 < p.nb; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + kx * p.nb + c0, r);
+                tmem_ld_wait();
+                float4 *o = reinterpret_cast<float4 *>(dst + (size_t)kx * 128 * p.nb + c0);
+#pragma unroll
+                for (int g = 0; g < 8; ++g)
+                    o[g] = any ? make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]), __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// gW[(co*cin_true + ci)*KK + ky*k + kx] += sum_split scratch[combo(ky,mblk,nblk)][split][kx][co%128][ci%nb]
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float *__restrict__ scratch, float *__restrict__ gW, int cin_true, int cin,
+                                                           int cout, int ksize, int nb, int n_mblk, int n_nblk, int splits) {
+    const int total = ksize * ksize * cout * cin;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int ci = idx % cin, co = (idx / cin) % cout, t = idx / (cin * cout);
+        if (ci >= cin_true) continue;
+        const int ky = t / ksize, kx = t - ky * ksize;
+        const int combo = (ky * n_mblk + co / 128) * n_nblk + ci / nb;
+        const float *src = scratch + (((size_t)combo * splits * ksize + kx) * 128 + (co & 127)) * nb + (ci % nb);
+        float s = 0.f;
+        for (int sp = 0; sp < splits; ++sp) s += src[(size_t)sp * ksize * 128 * nb];
+        gW[((size_t)co * cin_true + ci) * ksize * ksize + t] += s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-point / per-channel bias gradients from the blocked bf16 dZ image
+// ---------------------------------------------------------------------------------------------
+// ga[c][p] += sum_n dz[n][c][rho(p)] ; gb[c] += sum_{n,p} dz  (nn.Add gradBias, conv gradBias)
+__global__ void __launch_bounds__(384) bias_grad_bf16_kernel(const bf16 *__restrict__ dz, float *__restrict__ ga, float *__restrict__ gb,
+                                                             int n, int cout, int R, int pitch, int pad, int groups) {
+    __shared__ float red[12][8];
+    const int chunk = blockIdx.x, grp = blockIdx.y, p = threadIdx.x;
+    const int chunks = cout >> 3;
+    float s[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s[e] = 0.f;
+    if (p < DG_POINTS) {
+        const int x = p / DG_BOARD, y = p - x * DG_BOARD;
+        const int rho = (x + pad) * pitch + y + pad;
+        for (int i = grp; i < n; i += groups) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(dz + (((size_t)i * chunks + chunk) * R + rho) * 8));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                s[2 * e] += __uint_as_float(w[e] << 16);
+                s[2 * e + 1] += __uint_as_float(w[e] & 0xFFFF0000u);
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(&ga[(size_t)(chunk * 8 + e) * DG_POINTS + p], s[e]);
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        float v = s[e];
+#pragma unroll
+        for (int sh = 16; sh > 0; sh >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sh);
+        if ((p & 31) == 0) red[p >> 5][e] = v;
+    }
+    __syncthreads();
+    if (p < 8) {
+        float t = 0.f;
+        for (int w = 0; w < 12; ++w) t += red[w][p];
+        atomicAdd(&gb[chunk * 8 + p], t);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// head: last layer (C -> 1, 3x3) + bias + ReLU + log-softmax + NLL + top-1, and its backward
+// (experiments.lua:138-151 for the last layer; train.lua:8-10), one CTA per position.
+// ---------------------------------------------------------------------------------------------
+struct HeadParams {
+    const bf16 *in;          // H_{L-1}: [n][C/8][R][8], 3x3 geometry
+    const float *W, *b, *a;  // master parameters of the last layer: W[0][ci][3][3], b[0], a[0][19][19]
+    const int32_t *targets;  // may be NULL
+    float *logp, *loss_n;
+    int32_t *argmax;
+    bf16 *dz_out;            // dZ_{L-1}: [n][C/8][R_out][8] (NULL: forward only)
+    float *gW, *gb, *ga;     // gradient slots of the last layer
+    int n, C, R;
+    int R_out, pitch_out, pad_out;
+    float scale;
+};
+
+__device__ __forceinline__ float block_reduce_max(float v, float *sh) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, s));
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = sh[0];
+    for (int w = 1; w < 12; ++w) r = fmaxf(r, sh[w]);
+    __syncthreads();
+    return r;
+}
+__device__ __forceinline__ float block_reduce_sum(float v, float *sh) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = 0.f;
+    for (int w = 0; w < 12; ++w) r += sh[w];
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ float red[12];
+    __shared__ int redi[12];
+    __shared__ float dzs[DG_R3 + 32];            // dz of the 1-channel map by image row, zero at pads
+    const int pos = blockIdx.x, tid = threadIdx.x;
+    const int chunks = p.C >> 3;
+    const uint32_t img_bytes = (uint32_t)chunks * p.R * 16;
+    uint8_t *img = smem;
+    float *ws = reinterpret_cast<float *>(smem + ((img_bytes + 1023) & ~1023u));    // [9][C]
+    float *gws = ws + 9 * p.C;                                                         // [9][C] partial weight gradient
+
+    if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+    __syncthreads();
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&bar, img_bytes);
+        const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
+        for (int c = 0; c < chunks; ++c) bulk_g2s(img + (size_t)c * p.R * 16, src + (size_t)c * p.R * 16, (uint32_t)p.R * 16, &bar);
+    }
+    for (int i = tid; i < 9 * p.C; i += blockDim.x) {
+        const int t = i / p.C, c = i - t * p.C;
+        ws[i] = p.W[c * 9 + t];
+        gws[i] = 0.f;
+    }
+    for (int i = tid; i < DG_R3 + 32; i += blockDim.x) dzs[i] = 0.f;
+    __syncthreads();
+    mbar_wait(&bar, 0);
+
+    // ---- forward: one thread per image row 21..404
+    const int rho = 21 + tid;
+    const int xp = rho / 20, yp = rho - xp * 20;
+    const int x = xp - 1, y = yp - 1;
+    const bool valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+    const int pt = x * DG_BOARD + y;
+    float z = 0.f;
+    if (valid) {
+        float acc = 0.f;
+        for (int t = 0; t < 9; ++t) {
+            const int row = rho + (t / 3 - 1) * 20 + (t % 3 - 1);
+            const float *wt = ws + t * p.C;
+            for (int c = 0; c < chunks; ++c) {
+                const uint4 v = *reinterpret_cast<const uint4 *>(img + ((size_t)c * p.R + row) * 16);
+                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    acc = fmaf(__uint_as_float(w4[e] << 16), wt[c * 8 + 2 * e], acc);
+                    acc = fmaf(__uint_as_float(w4[e] & 0xFFFF0000u), wt[c * 8 + 2 * e + 1], acc);
+                }
+            }
+        }
+        z = acc + p.b[0] + p.a[pt];
+    }
+    const float h = valid ? fmaxf(z, 0.f) : -INFINITY;           // ReLU stays before LogSoftMax (experiments.lua:147)
+    const float mx = block_reduce_max(h, red);
+    const float se = block_reduce_sum(valid ? expf(h - mx) : 0.f, red);
+    const float lse = mx + logf(se);
+    const float lp = h - lse;
+    if (valid) p.logp[(size_t)pos * DG_POINTS + pt] = lp;
+    // first index of the maximum
+    {
+        int cand = (valid && h == mx) ? pt : 0x7fffffff;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, s));
+        if ((tid & 31) == 0) redi[tid >> 5] = cand;
+        __syncthreads();
+        if (tid == 0) {
+            int b = redi[0];
+            for (int w = 1; w < 12; ++w) b = min(b, redi[w]);
+            if (p.argmax) p.argmax[pos] = b;
+        }
+        __syncthreads();
+    }
+    const int tgt = p.targets ? p.targets[pos] : -1;
+    if (valid && pt == tgt && p.loss_n) p.loss_n[pos] = -lp;
+    if (!p.dz_out) return;
+
+    // ---- backward of LogSoftMax + NLL + ReLU on the 1-channel map
+    float dzv = 0.f;
+    if (valid && z > 0.f) dzv = p.scale * (expf(lp) - (pt == tgt ? 1.f : 0.f));
+    dzs[rho] = dzv;
+    if (valid) atomicAdd(&p.ga[pt], dzv);                        // nn.Add gradBias (361)
+    const float dsum = block_reduce_sum(dzv, red);               // also orders the dzs writes
+    if (tid == 0) atomicAdd(p.gb, dsum);                         // conv gradBias (1)
+
+    // ---- weight gradient of the last layer: gW[ci][t] += sum_rho dz[rho] * in[rho+off(t)][ci]
+    {
+        const int parts = blockDim.x / p.C;                      // C in {64,128,192} divides 384
+        const int ci = tid % p.C, part = tid / p.C;
+        if (part < parts) {
+            float acc[9];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) acc[t] = 0.f;
+            const uint8_t *col = img + (size_t)(ci >> 3) * p.R * 16 + (ci & 7) * 2;
+            for (int r = 21 + part; r < 400; r += parts) {
+                const float d = dzs[r];
+                if (d == 0.f) continue;
+#pragma unroll
+                for (int t = 0; t < 9; ++t) {
+                    const int row = r + (t / 3 - 1) * 20 + (t % 3 - 1);
+                    const uint16_t hv = *reinterpret_cast<const uint16_t *>(col + (size_t)row * 16);
+                    acc[t] = fmaf(d, __uint_as_float((uint32_t)hv << 16), acc[t]);
+                }
+            }
+#pragma unroll
+            for (int t = 0; t < 9; ++t) atomicAdd(&gws[t * p.C + ci], acc[t]);
+        }
+        __syncthreads();
+        for (int i = tid; i < 9 * p.C; i += blockDim.x) {
+            const int t = i / p.C, c = i - t * p.C;
+            atomicAdd(&p.gW[c * 9 + t], gws[i]);
+        }
+    }
+
+    // ---- input gradient + ReLU mask of layer L-1: dZ[rho][c] = (in[rho][c] > 0) * sum_t dz[rho - off(t)] * W[c][t]
+    if (valid) {
+        float d9[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) d9[t] = dzs[rho - ((t / 3 - 1) * 20 + (t % 3 - 1))];
+        const int rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
+        for (int c = 0; c < chunks; ++c) {
+            const uint4 hv = *reinterpret_cast<const uint4 *>(img + ((size_t)c * p.R + rho) * 16);
+            const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                float s = 0.f;
+#pragma unroll
+                for (int t = 0; t < 9; ++t) s = fmaf(d9[t], ws[t * p.C + c * 8 + e], s);
+                const uint32_t hh = (hw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                v[e] = (hh != 0 && (hh & 0x8000u) == 0) ? s : 0.f;
+            }
+            uint4 o;
+            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
+            o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
+            o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
+            *reinterpret_cast<uint4 *>(p.dz_out + (((size_t)pos * chunks + c) * p.R_out + rho_out) * 8) = o;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// staging + parameter packing
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int dg_src_point_d(int p, int sym) {
+    int x = p / DG_BOARD, y = p - x * DG_BOARD;
+    if (sym & 2) x = DG_BOARD - 1 - x;
+    if (sym & 4) y = DG_BOARD - 1 - y;
+    if (sym & 1) { int t = x; x = y; y = t; }
+    return x * DG_BOARD + y;
+}
+
+// raw records -> blocked bf16 input image [n][48/8][R][8] (planes 37..47 stay zero); same plane
+// definitions as encode.cu (dataloader.lua:50-92)
+__global__ void __launch_bounds__(384) encode_blocked_kernel(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ player,
+                                                            const uint8_t *__restrict__ rank, const uint8_t *__restrict__ sym,
+                                                            bf16 *__restrict__ out, int R, int pitch, int pad) {
+    const int n = blockIdx.x, p = threadIdx.x;
+    if (p >= DG_POINTS) return;
+    const int src = dg_src_point_d(p, sym ? sym[n] : 0);
+    const uint8_t *rec = raw + (size_t)n * DG_RAW_PLANES * DG_POINTS;
+    const int pl = player[n], rk = rank[n];
+    const int stone = rec[src], lib = rec[DG_POINTS + src], la = rec[(2 + pl - 1) * DG_POINTS + src];
+    const int kills = rec[(4 + pl - 1) * DG_POINTS + src], age = rec[6 * DG_POINTS + src], ladder = rec[(7 + pl - 1) * DG_POINTS + src];
+    unsigned long long m = 0;
+    m |= (unsigned long long)(stone == 0) << 0;
+    m |= (unsigned long long)(stone == pl) << 1;
+    m |= (unsigned long long)(stone == 3 - pl) << 2;
+    if (lib >= 1 && lib <= 3) m |= 1ull << (3 + lib - 1);
+    m |= (unsigned long long)(lib >= 4) << 6;
+    m |= (unsigned long long)(stone == 0 && la == 0) << 7;
+    if (la >= 1 && la <= 5) m |= 1ull << (7 + la);
+    m |= (unsigned long long)(la >= 6) << 13;
+    if (kills >= 1 && kills <= 6) m |= 1ull << (14 + kills - 1);
+    m |= (unsigned long long)(kills >= 7) << 20;
+    if (age >= 1 && age <= 5) m |= 1ull << (21 + age - 1);
+    m |= (unsigned long long)(ladder >= 1) << 26;
+    m |= 1ull << (27 + rk);
+    const int x = p / DG_BOARD, y = p - x * DG_BOARD;
+    const int rho = (x + pad) * pitch + y + pad;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) {
+        const uint32_t bits = (uint32_t)(m >> (c * 8)) & 0xFFu;
+        uint4 o;
+        // bf16 1.0 = 0x3F80
+        o.x = ((bits & 1) ? 0x3F80u : 0u) | ((bits & 2) ? 0x3F800000u : 0u);
+        o.y = ((bits & 4) ? 0x3F80u : 0u) | ((bits & 8) ? 0x3F800000u : 0u);
+        o.z = ((bits & 16) ? 0x3F80u : 0u) | ((bits & 32) ? 0x3F800000u : 0u);
+        o.w = ((bits & 64) ? 0x3F80u : 0u) | ((bits & 128) ? 0x3F800000u : 0u);
+        *reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8) = o;
+    }
+}
+
+// fp32 NCHW planes -> blocked bf16 input image
+__global__ void __launch_bounds__(384) planes_to_blocked_kernel(const float *__restrict__ planes, bf16 *__restrict__ out, int cin_true,
+                                                                int R, int pitch, int pad) {
+    const int n = blockIdx.x, p = threadIdx.x;
+    if (p >= DG_POINTS) return;
+    const int x = p / DG_BOARD, y = p - x * DG_BOARD;
+    const int rho = (x + pad) * pitch + y + pad;
+    for (int c = 0; c < 6; ++c) {
+        __align__(16) bf16 v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int ch = c * 8 + e;
+            v[e] = __float2bfloat16(ch < cin_true ? planes[((size_t)n * cin_true + ch) * DG_POINTS + p] : 0.f);
+        }
+        *reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+// master fp32 (Torch7 order) -> bf16 MMA operands of one layer:
+//   wf[t][ci/8][co][8]  = W[co][ci][t]            (forward B operand; ci >= cin_true -> 0)
+//   wd[t][co/8][ci][8]  = W[co][ci][KK-1-t]       (input-gradient B operand, taps flipped); may be NULL
+//   ab[c/8][rho][8]     = b[c] + a[c][x][y]       (fp32 epilogue bias in the OUTPUT geometry)
+__global__ void __launch_bounds__(256) pack_layer_kernel(const float *__restrict__ W, const float *__restrict__ b, const float *__restrict__ a,
+                                                         bf16 *__restrict__ wf, bf16 *__restrict__ wd, float *__restrict__ ab, int cin_true,
+                                                         int cin, int cout, int ksize, int R_out, int pitch_out, int pad_out) {
+    const int KK = ksize * ksize;
+    const int nwf = KK * cin * cout;
+    const int nab = cout * DG_POINTS;
+    const int stride = gridDim.x * blockDim.x;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nwf; idx += stride) {
+        const int e = idx & 7, co = (idx >> 3) % cout, c8 = (idx / (8 * cout)) % (cin >> 3), t = idx / (8 * cout * (cin >> 3));
+        const int ci = c8 * 8 + e;
+        wf[idx] = __float2bfloat16(ci < cin_true ? W[((size_t)co * cin_true + ci) * KK + t] : 0.f);
+    }
+    if (wd) {
+        for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nwf; idx += stride) {
+            const int e = idx & 7, ci = (idx >> 3) % cin, c8 = (idx / (8 * cin)) % (cout >> 3), t = idx / (8 * cin * (cout >> 3));
+            const int co = c8 * 8 + e;
+            wd[idx] = __float2bfloat16(ci < cin_true ? W[((size_t)co * cin_true + ci) * KK + (KK - 1 - t)] : 0.f);
+        }
+    }
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nab; idx += stride) {
+        const int c = idx / DG_POINTS, pt = idx - c * DG_POINTS;
+        const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
+        const int rho = (x + pad_out) * pitch_out + y + pad_out;
+        ab[((size_t)(c >> 3) * R_out + rho) * 8 + (c & 7)] = b[c] + a[idx];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+struct LayerOps {
+    bf16 *wf = nullptr, *wd = nullptr;
+    float *ab = nullptr;
+    int cin_pad = 0;
+};
+
+struct Bf16Path {
+    Geom g_first, g3;
+    int cin0_pad = 48;
+    bf16 *x0 = nullptr;                    // [B][6][R_first][8]
+    std::vector<bf16 *> h;                 // h[l], l = 1..L-1: [B][C/8][R3][8]
+    bf16 *dz[2] = {nullptr, nullptr};      // ping-pong dZ_l (3x3 geometry), l >= 2
+    bf16 *dz1 = nullptr;                   // dZ_1 in the first layer's geometry
+    std::vector<LayerOps> ops;             // per conv layer 0..L-2
+    float *scratch = nullptr;              // weight-gradient partial tiles
+    size_t scratch_bytes = 0;
+    int num_sms = 148;
+    bool head_bwd_done = false;
+};
+
+static size_t img_elems(int C, int R) { return (size_t)C * R; }
+
+static int conv_cfg(const dg_model *m, ConvParams &cp, int cin, int cout) {
+    cp.cin = cin; cp.cout = cout;
+    cp.nb = cout <= 128 ? cout : (cout % 96 == 0 ? 96 : (cout % 128 == 0 ? 128 : 64));
+    DG_REQUIRE(cout % cp.nb == 0 && cp.nb % 16 == 0, "bf16 path: unsupported channel count %d", cout);
+    cp.kp = cin % 64 == 0 ? 64 : cin;
+    DG_REQUIRE(cin % cp.kp == 0 && cp.kp % 16 == 0 && cin / cp.kp <= CONV_MAX_KPANELS, "bf16 path: unsupported input channel count %d", cin);
+    DG_REQUIRE(cp.ntiles * cp.nb <= 512, "bf16 path: accumulator does not fit TMEM");
+    return 0;
+}
+
+static int launch_conv(dg_model *m, ConvParams cp) {
+    dg_ctx *c = m->ctx;
+    const size_t img_bytes = ((size_t)(cp.cin / 8) * cp.R_in * 16 + 1023) & ~(size_t)1023;
+    const size_t stage = (size_t)cp.kp * cp.nb * 2;
+    const size_t budget = 227 * 1024 - 1024;       // static smem (barriers) lives in the remaining KB
+    DG_REQUIRE(img_bytes + 2 * stage <= budget, "bf16 path: image (%zu B) + weight ring do not fit shared memory", img_bytes);
+    int ns = (int)((budget - img_bytes) / stage);
+    if (ns > CONV_MAX_STAGES) ns = CONV_MAX_STAGES;
+    cp.nstages = ns;
+    const size_t smem = img_bytes + ns * stage;
+    const int grid = cp.n < m->bf->num_sms ? cp.n : m->bf->num_sms;
+    { dg_prof_scope _ps(c, cp.mode ? DG_K_DGRAD : (cp.ksize == 5 || cp.cin < cp.cout ? DG_K_CONV_FIRST : DG_K_CONV));
+    conv_umma_kernel<<<grid, 192, smem, c->stream>>>(cp);
+    }
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+
+struct WgradPlan { int nb, n_mblk, n_nblk, combos, splits, nstages; size_t smem, scratch_bytes; };
+
+static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const Geom &g, WgradPlan &w) {
+    w.nb = cin_pad;
+    while (ksize * w.nb > 512) w.nb /= 2;
+    DG_REQUIRE(w.nb % 16 == 0 && cin_pad % w.nb == 0 && w.nb <= 256, "bf16 path: unsupported weight-gradient N block for cin %d", cin_pad);
+    w.n_nblk = cin_pad / w.nb;
+    w.n_mblk = (cout + 127) / 128;
+    w.combos = ksize * w.n_mblk * w.n_nblk;
+    DG_REQUIRE(w.combos <= m->bf->num_sms, "bf16 path: too many weight-gradient tiles");
+    w.splits = m->bf->num_sms / w.combos;
+    const int rb_pad = (WG_RP + 2 * g.pad + 7) & ~7;
+    const size_t stage = 16 * WG_RP * 16 + (size_t)(w.nb / 8) * rb_pad * 16;
+    int ns = (int)((227 * 1024 - 1024) / stage);
+    if (ns > CONV_MAX_STAGES) ns = CONV_MAX_STAGES;
+    w.nstages = ns;
+    w.smem = ns * stage;
+    w.scratch_bytes = (size_t)w.combos * w.splits * ksize * 128 * w.nb * 4;
+    return 0;
+}
+
+int dg_bf16_create(dg_model *m) {
+    DG_REQUIRE(m->C % 16 == 0 && m->C >= 16 && m->C <= 256, "DG_PREC_BF16 needs channelSize %% 16 == 0 and <= 256 (got %d)", m->C);
+    DG_REQUIRE(384 % m->C == 0 || m->C > 384, "DG_PREC_BF16 head kernel needs channelSize dividing 384 (64, 96, 128, 192); got %d", m->C);
+    Bf16Path *b = new Bf16Path();
+    m->bf = b;
+    b->g_first = geom_for(m->k_first);
+    b->g3 = geom_for(3);
+    cudaDeviceProp prop;
+    DG_CUDA(cudaGetDeviceProperties(&prop, m->ctx->dev));
+    b->num_sms = prop.multiProcessorCount;
+    const size_t B = m->max_batch;
+    const int L = m->L, C = m->C;
+    cudaStream_t st = m->ctx->stream;
+    auto alloc0 = [&](void **p, size_t bytes) -> int {
+        DG_CUDA(cudaMalloc(p, bytes));
+        DG_CUDA(cudaMemsetAsync(*p, 0, bytes, st));
+        return 0;
+    };
+    if (int rc = alloc0((void **)&b->x0, B * img_elems(b->cin0_pad, b->g_first.rows) * 2)) return rc;
+    b->h.assign(L, nullptr);
+    for (int l = 1; l < L; ++l) if (int rc = alloc0((void **)&b->h[l], B * img_elems(C, DG_R3) * 2)) return rc;
+    for (int i = 0; i < 2; ++i) if (int rc = alloc0((void **)&b->dz[i], B * img_elems(C, DG_R3) * 2)) return rc;
+    if (int rc = alloc0((void **)&b->dz1, B * img_elems(C, b->g_first.rows) * 2)) return rc;
+    b->ops.resize(L - 1);
+    size_t scratch = 0;
+    for (int l = 0; l < L - 1; ++l) {
+        const LayerInfo &li = m->layers[l];
+        LayerOps &o = b->ops[l];
+        o.cin_pad = l == 0 ? b->cin0_pad : li.cin;
+        const size_t nw = (size_t)li.k * li.k * o.cin_pad * li.cout;
+        if (int rc = alloc0((void **)&o.wf, nw * 2)) return rc;
+        if (l > 0) if (int rc = alloc0((void **)&o.wd, nw * 2)) return rc;
+        if (int rc = alloc0((void **)&o.ab, (size_t)li.cout * DG_R3 * 4)) return rc;
+        WgradPlan w;
+        if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, l == 0 ? b->g_first : b->g3, w)) return rc;
+        if (w.scratch_bytes > scratch) scratch = w.scratch_bytes;
+    }
+    DG_CUDA(cudaMalloc((void **)&b->scratch, scratch));
+    b->scratch_bytes = scratch;
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
+    return 0;
+}
+
+void dg_bf16_destroy(dg_model *m) {
+    Bf16Path *b = m->bf;
+    if (!b) return;
+    cudaFree(b->x0);
+    for (bf16 *p : b->h) if (p) cudaFree(p);
+    cudaFree(b->dz[0]); cudaFree(b->dz[1]); cudaFree(b->dz1);
+    for (LayerOps &o : b->ops) { cudaFree(o.wf); if (o.wd) cudaFree(o.wd); cudaFree(o.ab); }
+    cudaFree(b->scratch);
+    delete b;
+    m->bf = nullptr;
+}
+
+int dg_bf16_params_changed(dg_model *m) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    for (int l = 0; l < m->L - 1; ++l) {
+        const LayerInfo &li = m->layers[l];
+        LayerOps &o = b->ops[l];
+        { dg_prof_scope _ps(c, DG_K_PACK);
+        pack_layer_kernel<<<b->num_sms * 2, 256, 0, c->stream>>>(m->params + li.offW, m->params + li.offB, m->params + li.offA, o.wf, o.wd, o.ab,
+                                                                 li.cin, o.cin_pad, li.cout, li.k, DG_R3, b->g3.pitch, b->g3.pad);
+                                                                 }
+        c->launches++;
+    }
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int dg_bf16_stage_raw(dg_model *m) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    { dg_prof_scope _ps(c, DG_K_ENCODE);
+    encode_blocked_kernel<<<m->n, 384, 0, c->stream>>>(m->d_raw, m->d_player, m->d_rank, m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad);
+    }
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int dg_bf16_stage_planes(dg_model *m) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    { dg_prof_scope _ps(c, DG_K_ENCODE);
+    planes_to_blocked_kernel<<<m->n, 384, 0, c->stream>>>(m->act[0], b->x0, m->in_planes, b->g_first.rows, b->g_first.pitch, b->g_first.pad);
+    }
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int launch_head(dg_model *m, bool backward, float scale) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    const LayerInfo &li = m->layers[m->L - 1];
+    HeadParams hp;
+    hp.in = b->h[m->L - 1];
+    hp.W = m->params + li.offW; hp.b = m->params + li.offB; hp.a = m->params + li.offA;
+    hp.targets = m->have_targets ? m->d_targets : nullptr;
+    hp.logp = m->d_logp; hp.loss_n = m->d_loss_n; hp.argmax = m->d_argmax;
+    // dZ_{L-1} lives in the geometry of layer L-1's own kernel: first-layer geometry when L-1 == 1
+    const bool into_first = (m->L - 1) == 1;
+    const Geom &go = into_first ? b->g_first : b->g3;
+    hp.dz_out = backward ? (into_first ? b->dz1 : b->dz[0]) : nullptr;
+    hp.gW = m->grads + li.offW; hp.gb = m->grads + li.offB; hp.ga = m->grads + li.offA;
+    hp.n = m->n; hp.C = m->C; hp.R = DG_R3;
+    hp.R_out = go.rows; hp.pitch_out = go.pitch; hp.pad_out = go.pad;
+    hp.scale = scale;
+    const size_t smem = (((size_t)(m->C / 8) * DG_R3 * 16 + 1023) & ~(size_t)1023) + (size_t)18 * m->C * 4;
+    DG_REQUIRE(smem <= 227 * 1024 - 4096, "bf16 path: head image does not fit shared memory (C=%d)", m->C);
+    { dg_prof_scope _ps(c, DG_K_HEAD);
+    head_bf16_kernel<<<m->n, 384, smem, c->stream>>>(hp);
+    }
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int dg_bf16_forward(dg_model *m) {
+    Bf16Path *b = m->bf;
+    for (int l = 0; l < m->L - 1; ++l) {
+        const LayerInfo &li = m->layers[l];
+        const Geom &gi = l == 0 ? b->g_first : b->g3;
+        ConvParams cp{};
+        cp.in = l == 0 ? b->x0 : b->h[l];
+        cp.w = b->ops[l].wf; cp.out = b->h[l + 1]; cp.bias = b->ops[l].ab; cp.mask = nullptr;
+        cp.n = m->n;
+        cp.R_in = gi.rows; cp.pitch_in = gi.pitch; cp.pad_in = gi.pad; cp.ksize = li.k; cp.first = gi.first; cp.ntiles = gi.ntiles;
+        cp.R_out = DG_R3; cp.pitch_out = b->g3.pitch; cp.pad_out = b->g3.pad;
+        cp.R_mask = cp.pitch_mask = cp.pad_mask = 0;
+        cp.mode = 0;
+        if (int rc = conv_cfg(m, cp, b->ops[l].cin_pad, li.cout)) return rc;
+        if (int rc = launch_conv(m, cp)) return rc;
+    }
+    b->head_bwd_done = false;
+    return launch_head(m, false, 0.f);
+}
+
+int dg_bf16_backward(dg_model *m, float scale) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    if (int rc = launch_head(m, true, scale)) return rc;
+    int cur = 0;                                           // dZ_{L-1} is in dz[0] (or dz1 when L-1 == 1)
+    for (int l = m->L - 2; l >= 0; --l) {                  // conv layer index l (0-based) = layer l+1
+        const LayerInfo &li = m->layers[l];
+        const LayerOps &o = b->ops[l];
+        const Geom &g = l == 0 ? b->g_first : b->g3;
+        const bf16 *dzl = l == 0 ? b->dz1 : b->dz[cur];
+        {
+            const int groups = 8;
+            { dg_prof_scope _ps(c, DG_K_BIAS_GRAD);
+            bias_grad_bf16_kernel<<<dim3(li.cout / 8, groups), 384, 0, c->stream>>>(dzl, m->grads + li.offA, m->grads + li.offB, m->n, li.cout,
+                                                                                   g.rows, g.pitch, g.pad, groups);
+                                                                                   }
+            c->launches++;
+        }
+        {
+            WgradPlan w;
+            if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
+            WgradParams wp{};
+            wp.dz = dzl; wp.x = l == 0 ? b->x0 : b->h[l]; wp.scratch = b->scratch;
+            wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
+            wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
+            wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
+            { dg_prof_scope _ps(c, DG_K_WGRAD);
+            wgrad_umma_kernel<<<w.combos * w.splits, 192, w.smem, c->stream>>>(wp);
+            }
+            c->launches++;
+            { dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE);
+            wgrad_reduce_kernel<<<b->num_sms * 4, 256, 0, c->stream>>>(b->scratch, m->grads + li.offW, li.cin, o.cin_pad, li.cout, li.k, w.nb,
+                                                                       w.n_mblk, w.n_nblk, w.splits);
+                                                                       }
+            c->launches++;
+        }
+        if (l >= 1) {
+            // dZ_{l} -> dZ_{l-1}: transposed conv with flipped taps, masked by ReLU of layer l's input h_l
+            const bool into_first = (l - 1) == 0;
+            const Geom &go = into_first ? b->g_first : b->g3;
+            ConvParams cp{};
+            cp.in = dzl; cp.w = o.wd; cp.out = into_first ? b->dz1 : b->dz[cur ^ 1]; cp.bias = nullptr; cp.mask = b->h[l];
+            cp.n = m->n;
+            cp.R_in = DG_R3; cp.pitch_in = b->g3.pitch; cp.pad_in = b->g3.pad; cp.ksize = 3; cp.first = b->g3.first; cp.ntiles = b->g3.ntiles;
+            cp.R_out = go.rows; cp.pitch_out = go.pitch; cp.pad_out = go.pad;
+            cp.R_mask = DG_R3; cp.pitch_mask = b->g3.pitch; cp.pad_mask = b->g3.pad;
+            cp.mode = 1;
+            if (int rc = conv_cfg(m, cp, li.cout, li.cin)) return rc;
+            if (int rc = launch_conv(m, cp)) return rc;
+            cur ^= 1;
+        }
+    }
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -80,21 +80,27 @@ __global__ void labels_kernel(const uint8_t *__restrict__ x, const uint8_t *__re
 
 int dg_launch_encode_f32(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint8_t *rank, const uint8_t *sym, int n, float *out) {
     if (n <= 0) return 0;
+    { dg_prof_scope _ps(ctx, DG_K_ENCODE);
     encode_f32_kernel<<<n, 384, 0, ctx->stream>>>(raw, player, rank, sym, out);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
 }
 int dg_launch_encode_bits(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint8_t *rank, const uint8_t *sym, int n, uint32_t *out) {
     if (n <= 0) return 0;
+    { dg_prof_scope _ps(ctx, DG_K_ENCODE);
     encode_bits_kernel<<<n, 384, 0, ctx->stream>>>(raw, player, rank, sym, out);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
 }
 int dg_launch_labels(dg_ctx *ctx, const uint8_t *x, const uint8_t *y, const uint8_t *sym, int n, int32_t *out) {
     if (n <= 0) return 0;
+    { dg_prof_scope _ps(ctx, DG_K_OTHER);
     labels_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(x, y, sym, n, out);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;

@@ -87,7 +87,9 @@ __global__ void __launch_bounds__(256) loss_reduce_kernel(const float *__restric
 int dg_launch_logsoftmax_nll(dg_ctx *ctx, const float *h_last, const int32_t *targets, float *logp, float *loss_n,
                              float *dz_last, int32_t *argmax, int n, float scale) {
     if (n <= 0) return 0;
+    { dg_prof_scope _ps(ctx, DG_K_HEAD);
     logsoftmax_nll_kernel<<<(n + 3) / 4, 128, 0, ctx->stream>>>(h_last, targets, logp, loss_n, dz_last, argmax, n, scale);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
@@ -95,7 +97,9 @@ int dg_launch_logsoftmax_nll(dg_ctx *ctx, const float *h_last, const int32_t *ta
 int dg_launch_loss_reduce(dg_ctx *ctx, const float *loss_n, const int32_t *argmax, const int32_t *targets, int n,
                           float *loss_out, int *errors_out) {
     if (n <= 0) return 0;
+    { dg_prof_scope _ps(ctx, DG_K_OTHER);
     loss_reduce_kernel<<<1, 256, 0, ctx->stream>>>(loss_n, argmax, targets, n, loss_out, errors_out);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;

@@ -27,7 +27,9 @@ int dg_launch_sgd(dg_ctx *ctx, float *p, const float *g, size_t n, float rate) {
     size_t blocks = (n / 4 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks == 0) blocks = 1;
+    { dg_prof_scope _ps(ctx, DG_K_SGD);
     sgd_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(p, g, n, -rate);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
@@ -36,7 +38,9 @@ int dg_launch_fill(dg_ctx *ctx, float *p, size_t n, float v) {
     if (n == 0) return 0;
     size_t blocks = (n + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
+    { dg_prof_scope _ps(ctx, DG_K_OTHER);
     fill_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(p, n, v);
+    }
     ctx->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;

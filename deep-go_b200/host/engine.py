@@ -6,6 +6,10 @@ import deepgo_b200 as _dg
 from deepgo_b200 import ffi, check, DG_PREC_FP32, DG_PREC_BF16, DG_FMT_F32_NCHW, DG_FMT_BITPLANES  # noqa: F401
 
 
+KERNEL_KINDS = ["encode", "conv_first", "conv", "dgrad", "wgrad", "wgrad_reduce", "bias_grad", "head", "sgd", "pack",
+                "allreduce", "other"]
+
+
 def _u8(a):
     a = np.ascontiguousarray(a, dtype=np.uint8)
     return a, ffi.cast("const uint8_t *", a.ctypes.data)
@@ -54,6 +58,20 @@ class Context:
         ms = ffi.new("float *")
         check(self.L.dg_timer_stop(self.h, ms))
         return float(ms[0])
+
+    def prof_begin(self):
+        check(self.L.dg_prof_begin(self.h))
+
+    def prof_end(self):
+        """-> {kind: (total_ms, launches)} for the launches since prof_begin"""
+        check(self.L.dg_prof_end(self.h))
+        out = {}
+        for k, name in enumerate(KERNEL_KINDS):
+            ms = ffi.new("float *"); n = ffi.new("long long *")
+            check(self.L.dg_prof_get(self.h, k, ms, n))
+            if n[0]:
+                out[name] = (float(ms[0]), int(n[0]))
+        return out
 
     def flush_l2(self):
         check(self.L.dg_ctx_flush_l2(self.h))
@@ -122,6 +140,9 @@ class Model:
         sa, sp = _opt_u8(sym); xa, xp = _opt_u8(x); ya, yp = _opt_u8(y)
         self.n = len(pa)
         check(self.L.dg_model_set_batch_raw(self.h, rp, pp, kp, sp, xp, yp, self.n))
+
+    def encode_resident(self):
+        check(self.L.dg_model_encode_resident(self.h))
 
     def set_batch_planes(self, planes, targets0=None):
         a = np.ascontiguousarray(planes, dtype=np.float32)

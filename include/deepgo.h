@@ -50,8 +50,15 @@ int dg_ctx_launch_count(dg_ctx *ctx, long long *out);
 /* CUDA-event timer on the context's stream (sys.clock() pairs, train.lua:91,94,113,137) */
 int dg_timer_start(dg_ctx *ctx);
 int dg_timer_stop(dg_ctx *ctx, float *ms_out);
-/* write `bytes` of device memory (L2 flush between timed iterations) */
+/* overwrite a 256 MB device buffer (L2 flush between timed iterations) */
 int dg_ctx_flush_l2(dg_ctx *ctx);
+/* per-kernel device timing for the roofline report: between dg_prof_begin and dg_prof_end every launch
+ * is bracketed by CUDA events on the context's stream; dg_prof_get returns the summed duration and the
+ * launch count of one kernel kind (0 encode, 1 first conv, 2 conv, 3 input-gradient conv, 4 weight gradient,
+ * 5 weight-gradient reduction, 6 bias gradient, 7 head, 8 SGD, 9 operand pack, 10 allreduce, 11 other). */
+int dg_prof_begin(dg_ctx *ctx);
+int dg_prof_end(dg_ctx *ctx);
+int dg_prof_get(dg_ctx *ctx, int kind, float *ms_total, long long *launches);
 
 /* ---- data parallel (nn.DataParallelTable(1), experiments.lua:155-168) ---------------------- */
 /* One process per GPU.  Rank 0 calls dg_dp_unique_id and ships the 128 bytes to the other ranks
@@ -107,6 +114,9 @@ int dg_model_set_global_batch(dg_model *m, int global_batch);
 int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
                            const uint8_t *sym, const uint8_t *x, const uint8_t *y, int n);
 int dg_model_set_batch_planes(dg_model *m, const float *planes, const int32_t *targets0, int n);
+/* re-run the on-device encode of the records staged by the last dg_model_set_batch_raw (inputs already
+ * resident in HBM; no host copy) */
+int dg_model_encode_resident(dg_model *m);
 
 /* model:forward (train.lua:6,28): log-probs float[n][361] to host if logprobs_out != NULL */
 int dg_forward(dg_model *m, float *logprobs_out);

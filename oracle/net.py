@@ -78,7 +78,8 @@ def forward(flat, x, num_layers, channel_size, quant=None):
     hs, zs = [h], []
     for i, (W, b, a) in enumerate(layers):
         k = W.shape[-1]
-        z = F.conv2d(h, _q(W, quant), None, padding=(k - 1) // 2) + b.view(1, -1, 1, 1) + a.unsqueeze(0)
+        Wq = _q(W, quant) if i < len(layers) - 1 else W         # the 1-channel head keeps fp32 weights on the GPU
+        z = F.conv2d(h, Wq, None, padding=(k - 1) // 2) + b.view(1, -1, 1, 1) + a.unsqueeze(0)
         zs.append(z)
         h = torch.relu(z)
         if i < len(layers) - 1:
@@ -116,7 +117,8 @@ def loss_and_grads(flat, x, targets0, num_layers, channel_size, quant=None, grad
         gb.copy_(dz.sum((0, 2, 3)))                               # conv bias: sum over batch and space
         gW.copy_(torch.nn.grad.conv2d_weight(hs[i], W.shape, dz, padding=(k - 1) // 2))
         if i > 0:
-            dh = torch.nn.grad.conv2d_input(hs[i].shape, _q(W, quant), dz, padding=(k - 1) // 2)
+            Wq = _q(W, quant) if i < num_layers - 1 else W
+            dh = torch.nn.grad.conv2d_input(hs[i].shape, Wq, dz, padding=(k - 1) // 2)
     return float(loss), grads, logp
 
 

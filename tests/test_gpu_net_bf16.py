@@ -1,0 +1,131 @@
+"""-m gpu: tcgen05 bf16 path through the C ABI.
+
+Two comparisons, tolerances stated here:
+  (1) against the oracle with the SAME rounding points (weights, stored activations and stored dZ rounded to
+      bf16, fp32/fp64 accumulation): forward log-probs 2e-3 abs, per-tensor gradient error 2e-2 relative
+      (a ReLU mask can flip on a value that rounds differently; everything else is accumulation order);
+  (2) against the un-rounded fp64 reference arithmetic: log-probs 5e-2 abs, top-1 agreement >= 90% on
+      He-scaled weights (north_star: "within a stated fp32 (tf32/bf16) tolerance, top-1 move agreement").
+"""
+import numpy as np
+import pytest
+import torch
+
+from tests import gpu_util as U
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(L, C, n, flat):
+    from deepgo_b200.host import engine
+    m = engine.Model(U.ctx(), L, C, engine.DG_PREC_BF16, max_batch=n)
+    m.set_params(flat.numpy())
+    return m
+
+
+def _check(golden, L, C, n, kind, seed, gtol=2e-2):
+    from oracle import net
+    b = U.sample(golden, n, seed)
+    x, t = U.oracle_batch(b)
+    flat = net.init_params(L, C, seed + 2, kind)
+    xq = torch.from_numpy(x)
+    loss_q, g_q, logp_q = net.loss_and_grads(flat, xq, t, L, C, quant="bf16")
+    loss_r, g_r, logp_r = net.loss_and_grads(flat, xq, t, L, C)
+    m = _model(L, C, n, flat)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    logp = m.forward()
+    assert np.isfinite(logp).all()
+    assert np.abs(logp - logp_q.numpy()).max() < 2e-3
+    assert np.abs(logp - logp_r.numpy()).max() < 5e-2
+    assert np.allclose(np.exp(logp.astype(np.float64)).sum(1), 1.0, atol=1e-4)
+    assert np.array_equal(m.argmax(), logp.argmax(1))
+    if kind == "he":
+        assert (logp.argmax(1) == logp_r.numpy().argmax(1)).mean() >= 0.9
+    m.zero_grads()
+    loss = m.loss_backward()
+    assert abs(loss - loss_q) < 2e-3
+    g = torch.from_numpy(m.get_grads())
+    for li, ((W, bb, a), (Wq, bq, aq)) in enumerate(zip(net.split_params(g, L, C), net.split_params(g_q, L, C))):
+        assert U.rel(W, Wq) < gtol, ("W", li, U.rel(W, Wq))
+        assert U.rel(a, aq) < gtol, ("a", li, U.rel(a, aq))
+        assert U.rel(bb, bq) < gtol, ("b", li, U.rel(bb, bq))
+    return m, b, flat
+
+
+def test_localtest_shape_c1(golden):                 # 3 x 64, batch 2 (localtest.lua)
+    _check(golden, 3, 64, 2, "he", 0)
+
+
+def test_c2_shape_small_batch(golden):               # 12 x 128 (BASELINE config 2 architecture), 6 positions
+    _check(golden, 12, 128, 6, "he", 1, gtol=5e-2)
+
+
+def test_192_filters(golden):                        # c3 architecture width, shallow
+    _check(golden, 4, 192, 3, "he", 2)
+
+
+def test_torch7_init_6x64(golden):
+    _check(golden, 6, 64, 5, "torch7", 3)
+
+
+def test_multi_position_per_cta_and_ragged_batch(golden):
+    """more positions than SMs: every CTA loops over several positions; batch not a multiple of anything"""
+    from oracle import net
+    L, C, n = 3, 64, 301
+    b = U.sample(golden, n, 5)
+    x, t = U.oracle_batch(b)
+    flat = net.init_params(L, C, 11, "he")
+    logp_q, _ = net.forward(flat, torch.from_numpy(x), L, C, quant="bf16")
+    m = _model(L, C, n, flat)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    logp = m.forward()
+    assert np.abs(logp - logp_q.numpy()).max() < 2e-3
+
+
+def test_planes_staging_and_train_steps(golden):
+    from oracle import net
+    L, C, n = 4, 64, 8
+    flat = net.init_params(L, C, 9, "he")
+    m = _model(L, C, n, flat)
+    rate = 0.05
+    for step in range(4):
+        b = U.sample(golden, n, 200 + step)
+        x, t = U.oracle_batch(b)
+        loss_q, g_q, _ = net.loss_and_grads(flat, torch.from_numpy(x), t, L, C, quant="bf16")
+        if step % 2:
+            m.set_batch_planes(x.astype(np.float32), t)
+        else:
+            m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+        loss = m.train_step(rate)
+        assert abs(loss - loss_q) < 5e-3, step
+        rate = net.sgd_step(flat, g_q, rate, 1e-7)
+    assert U.rel(m.get_params(), flat.numpy()) < 1e-3
+
+
+def test_full_size_properties(golden):
+    """c2 at its full batch (128): properties that need no oracle run -- probabilities sum to 1, the loss of a
+    repeated step decreases, gradients of a duplicated batch equal those of the single batch."""
+    from oracle import net
+    L, C, n = 12, 128, 128
+    flat = net.init_params(L, C, 4, "he")
+    m = _model(L, C, n, flat)
+    b = U.sample(golden, n, 7)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    logp = m.forward()
+    assert np.isfinite(logp).all()
+    assert np.allclose(np.exp(logp.astype(np.float64)).sum(1), 1.0, atol=1e-4)
+    m.zero_grads(); m.loss_backward()
+    g_full = m.get_grads()
+    # mean gradient of [batch, batch] equals the mean gradient of batch (linearity of the batch reduction)
+    half = {k: np.concatenate([v[:64], v[:64]]) for k, v in b.items()}
+    m.set_batch_raw(half["raw"], half["player"], half["rank"], half["sym"], half["x"], half["y"])
+    m.forward(False); m.zero_grads(); m.loss_backward()
+    g_dup = m.get_grads()
+    one = {k: v[:64] for k, v in b.items()}
+    m.set_batch_raw(one["raw"], one["player"], one["rank"], one["sym"], one["x"], one["y"])
+    m.forward(False); m.zero_grads(); m.loss_backward()
+    g_one = m.get_grads()
+    assert U.rel(g_dup, g_one) < 1e-3
+    assert np.linalg.norm(g_full) > 0
+    l0 = m.train_step(0.02); l1 = m.train_step(0.02); l2 = m.train_step(0.02)
+    assert l2 < l0
