@@ -77,7 +77,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                       "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             pass
 
@@ -183,10 +183,10 @@ def run_ours(args, rank, local_rank, world):
 
     # ---------------- device-resident throughput ("value") ----------------
     m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    sampler = ClockSampler(local_rank) if rank == 0 else None      # nvidia-smi needs a moment to start: begin before warm-up
     for _ in range(max(3, args.warmup)):
         m.encode_resident(); m.train_step(rate, want_loss=False)
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     l0 = ctx.launch_count()
     total_ms, launches = 0.0, 0
     for _ in range(args.steps):
@@ -268,8 +268,8 @@ def run_ours(args, rank, local_rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

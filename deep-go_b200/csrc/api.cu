@@ -439,8 +439,11 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     DG_CUDA(cudaSetDevice(c->dev));
     DG_REQUIRE(m->have_targets, "dg_train_step: the staged batch has no targets");
     DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));          // train.lua:5
-    if (int rc = forward_impl(m)) return rc;                               // train.lua:6
-    if (int rc = backward_impl(m)) return rc;                              // train.lua:8-10
+    m->fused_step = true;
+    int rc_f = forward_impl(m);                                            // train.lua:6
+    if (!rc_f) rc_f = backward_impl(m);                                    // train.lua:8-10
+    m->fused_step = false;
+    if (rc_f) return rc_f;
     if (c->world > 1) if (int rc = dg_dp_allreduce(c, m->grads, m->P)) return rc;
     if (int rc = dg_sgd_step(m, rate)) return rc;                          // train.lua:131
     if (loss_out) return read_loss(m, loss_out, nullptr);

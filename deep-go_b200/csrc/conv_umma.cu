@@ -119,6 +119,9 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
         if (lane == 0) {
             const uint32_t idesc = make_idesc_bf16(128, p.nb, 0, 0);
             const uint32_t img_a = smem_u32(img), ring_a = smem_u32(ring);
+            const uint32_t a_lo0 = desc_lo(img_a, (uint32_t)p.R_in * 16), hi = desc_hi(128);
+            const uint32_t a_kstep = 2u * p.R_in, b_kstep = 2u * p.nb;
+            const int ksteps = p.kp >> 4;
             uint32_t it = 0, j = 0, a = 0;
             for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
@@ -132,15 +135,16 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
                             tc_fence_after();
                             const int ky = t / p.ksize, kx = t - ky * p.ksize;
                             const int toff = (ky - p.pad_in) * p.pitch_in + (kx - p.pad_in);
-                            const uint32_t b_base = ring_a + s * stage_bytes;
-                            for (int tile = 0; tile < p.ntiles; ++tile) {
-                                const uint32_t a_row = (uint32_t)(p.first + tile * 128 + toff);
-                                for (int ks = 0; ks < (p.kp >> 4); ++ks) {
-                                    const uint32_t a_addr = img_a + ((uint32_t)(k * chunks_kp + ks * 2) * p.R_in + a_row) * 16;
-                                    const uint64_t ad = make_desc(a_addr, (uint32_t)p.R_in * 16, 128);
-                                    const uint64_t bd = make_desc(b_base + (uint32_t)(ks * 2) * p.nb * 16, (uint32_t)p.nb * 16, 128);
-                                    mma_bf16(tmem_base + tile * p.nb, ad, bd, idesc, (k | t | ks) != 0);
-                                }
+                            // descriptor low words in 16-byte units: +1 per image row, +R_in per channel chunk
+                            uint32_t a_tile = a_lo0 + (uint32_t)(k * chunks_kp) * p.R_in + (uint32_t)(p.first + toff);
+                            const uint32_t b_lo0 = desc_lo(ring_a + s * stage_bytes, (uint32_t)p.nb * 16);
+                            uint32_t d_tmem = tmem_base;
+                            const uint32_t acc0 = (k | t) != 0;
+                            for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
+                                uint32_t a_lo = a_tile, b_lo = b_lo0;
+#pragma unroll 4
+                                for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep)
+                                    mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, acc0 | (uint32_t)ks);
                             }
                             mma_commit(&w_empty[s]);
                         }
@@ -165,28 +169,41 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
                     const int x = xp - p.pad_in, y = yp - p.pad_in;
                     const bool valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
                     const int rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
+                    const int rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
                     for (int c0 = 0; c0 < p.nb; c0 += 32) {
                         uint32_t r[32];
                         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+                        const int chunk0 = (nbk * p.nb + c0) >> 3;
+                        float4 bv[8];
+                        uint4 mk[4];
+                        if (valid) {
+                            if (p.mode == 0) {
+#pragma unroll
+                                for (int g = 0; g < 4; ++g) {
+                                    const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)(chunk0 + g) * p.R_out + rho_out) * 8);
+                                    bv[2 * g] = __ldg(bp); bv[2 * g + 1] = __ldg(bp + 1);
+                                }
+                            } else {
+#pragma unroll
+                                for (int g = 0; g < 4; ++g)
+                                    mk[g] = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
+                            }
+                        }
                         tmem_ld_wait();
                         if (valid) {
 #pragma unroll
                             for (int g = 0; g < 4; ++g) {
-                                const int chunk = (nbk * p.nb + c0) / 8 + g;
                                 float v[8];
 #pragma unroll
                                 for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
                                 if (p.mode == 0) {
-                                    const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)chunk * p.R_out + rho_out) * 8);
-                                    const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1);
+                                    const float4 b0 = bv[2 * g], b1 = bv[2 * g + 1];
                                     v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f);
                                     v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
                                     v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f);
                                     v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
                                 } else {
-                                    const int rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
-                                    const uint4 mk = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk) * p.R_mask + rho_m) * 8));
-                                    const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+                                    const uint32_t mw[4] = {mk[g].x, mk[g].y, mk[g].z, mk[g].w};
 #pragma unroll
                                     for (int e = 0; e < 8; ++e) {
                                         const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
@@ -199,7 +216,7 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
                                 __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
                                 o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
                                 o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
-                                *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk) * p.R_out + rho_out) * 8) = o;
+                                *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk0 + g) * p.R_out + rho_out) * 8) = o;
                             }
                         }
                     }
@@ -286,18 +303,21 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = make_idesc_bf16(128, p.nb, 1, 1);
+            const uint32_t hi_a = desc_hi(WG_RP * 16), hi_b = desc_hi((uint32_t)rb_pad * 16);
             uint32_t it = 0;
             for (int u = split; u < units; u += p.splits, ++it) {
                 const int s = it % p.nstages;
                 mbar_wait(&s_full[s], (it / p.nstages) & 1);
                 tc_fence_after();
                 const uint32_t sa = smem_u32(smem) + s * stage_bytes, sb = sa + a_bytes;
-                for (int kx = 0; kx < p.ksize; ++kx)
-                    for (int ks = 0; ks < WG_RP / 16; ++ks) {
-                        const uint64_t ad = make_desc(sa + ks * 256, 128, WG_RP * 16);
-                        const uint64_t bd = make_desc(sb + (kx + ks * 16) * 16, 128, (uint32_t)rb_pad * 16);
-                        mma_bf16(tmem_base + kx * p.nb, ad, bd, idesc, (it | ks) != 0);
-                    }
+                const uint32_t a_lo0 = desc_lo(sa, 128), b_lo0 = desc_lo(sb, 128);
+                uint32_t d_tmem = tmem_base;
+                for (int kx = 0; kx < p.ksize; ++kx, d_tmem += p.nb) {
+                    uint32_t a_lo = a_lo0, b_lo = b_lo0 + kx;
+#pragma unroll
+                    for (int ks = 0; ks < WG_RP / 16; ++ks, a_lo += 16, b_lo += 16)
+                        mma_bf16(d_tmem, desc_join(a_lo, hi_a), desc_join(b_lo, hi_b), idesc, it | (uint32_t)ks);
+                }
                 mma_commit(&s_empty[s]);
             }
             mma_commit(&acc_full);
@@ -311,13 +331,16 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
         for (int kx = 0; kx < p.ksize; ++kx)
             for (int c0 = 0; c0 < p.nb; c0 += 32) {
                 uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + kx * p.nb + c0, r);
+                const int ncol = min(32, p.nb - c0);              // nb is a multiple of 16
+                const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + kx * p.nb + c0;
+                if (ncol == 32) tmem_ld32(ta, r); else tmem_ld16(ta, r);
                 tmem_ld_wait();
                 float4 *o = reinterpret_cast<float4 *>(dst + (size_t)kx * 128 * p.nb + c0);
 #pragma unroll
                 for (int g = 0; g < 8; ++g)
-                    o[g] = any ? make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]), __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]))
-                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (g * 4 < ncol)
+                        o[g] = any ? make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]), __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]))
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
             }
     }
     tc_fence_before();
@@ -335,9 +358,15 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float *__restri
         const int ky = t / ksize, kx = t - ky * ksize;
         const int combo = (ky * n_mblk + co / 128) * n_nblk + ci / nb;
         const float *src = scratch + (((size_t)combo * splits * ksize + kx) * 128 + (co & 127)) * nb + (ci % nb);
-        float s = 0.f;
-        for (int sp = 0; sp < splits; ++sp) s += src[(size_t)sp * ksize * 128 * nb];
-        gW[((size_t)co * cin_true + ci) * ksize * ksize + t] += s;
+        const size_t st = (size_t)ksize * 128 * nb;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int sp = 0;
+        for (; sp + 4 <= splits; sp += 4) {
+            s0 += src[(size_t)sp * st]; s1 += src[(size_t)(sp + 1) * st];
+            s2 += src[(size_t)(sp + 2) * st]; s3 += src[(size_t)(sp + 3) * st];
+        }
+        for (; sp < splits; ++sp) s0 += src[(size_t)sp * st];
+        gW[((size_t)co * cin_true + ci) * ksize * ksize + t] += (s0 + s1) + (s2 + s3);
     }
 }
 
@@ -356,6 +385,7 @@ __global__ void __launch_bounds__(384) bias_grad_bf16_kernel(const bf16 *__restr
     if (p < DG_POINTS) {
         const int x = p / DG_BOARD, y = p - x * DG_BOARD;
         const int rho = (x + pad) * pitch + y + pad;
+#pragma unroll 4
         for (int i = grp; i < n; i += groups) {
             const uint4 v = __ldg(reinterpret_cast<const uint4 *>(dz + (((size_t)i * chunks + chunk) * R + rho) * 8));
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
@@ -637,9 +667,19 @@ __global__ void __launch_bounds__(384) planes_to_blocked_kernel(const float *__r
 //   wf[t][ci/8][co][8]  = W[co][ci][t]            (forward B operand; ci >= cin_true -> 0)
 //   wd[t][co/8][ci][8]  = W[co][ci][KK-1-t]       (input-gradient B operand, taps flipped); may be NULL
 //   ab[c/8][rho][8]     = b[c] + a[c][x][y]       (fp32 epilogue bias in the OUTPUT geometry)
-__global__ void __launch_bounds__(256) pack_layer_kernel(const float *__restrict__ W, const float *__restrict__ b, const float *__restrict__ a,
-                                                         bf16 *__restrict__ wf, bf16 *__restrict__ wd, float *__restrict__ ab, int cin_true,
-                                                         int cin, int cout, int ksize, int R_out, int pitch_out, int pad_out) {
+struct PackLayer {
+    const float *W, *b, *a;
+    bf16 *wf, *wd;
+    float *ab;
+    int cin_true, cin, cout, ksize;
+};
+
+__global__ void __launch_bounds__(256) pack_layer_kernel(const PackLayer *__restrict__ table, int R_out, int pitch_out, int pad_out) {
+    const PackLayer pl = table[blockIdx.y];
+    const float *__restrict__ W = pl.W, *__restrict__ b = pl.b, *__restrict__ a = pl.a;
+    bf16 *__restrict__ wf = pl.wf, *__restrict__ wd = pl.wd;
+    float *__restrict__ ab = pl.ab;
+    const int cin_true = pl.cin_true, cin = pl.cin, cout = pl.cout, ksize = pl.ksize;
     const int KK = ksize * ksize;
     const int nwf = KK * cin * cout;
     const int nab = cout * DG_POINTS;
@@ -681,6 +721,7 @@ struct Bf16Path {
     bf16 *dz[2] = {nullptr, nullptr};      // ping-pong dZ_l (3x3 geometry), l >= 2
     bf16 *dz1 = nullptr;                   // dZ_1 in the first layer's geometry
     std::vector<LayerOps> ops;             // per conv layer 0..L-2
+    PackLayer *pack_table = nullptr;       // device copy, one entry per conv layer
     float *scratch = nullptr;              // weight-gradient partial tiles
     size_t scratch_bytes = 0;
     int num_sms = 148;
@@ -776,6 +817,18 @@ int dg_bf16_create(dg_model *m) {
         if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, l == 0 ? b->g_first : b->g3, w)) return rc;
         if (w.scratch_bytes > scratch) scratch = w.scratch_bytes;
     }
+    {
+        std::vector<PackLayer> tab(L - 1);
+        for (int l = 0; l < L - 1; ++l) {
+            const LayerInfo &li = m->layers[l];
+            tab[l].W = m->params + li.offW; tab[l].b = m->params + li.offB; tab[l].a = m->params + li.offA;
+            tab[l].wf = b->ops[l].wf; tab[l].wd = b->ops[l].wd; tab[l].ab = b->ops[l].ab;
+            tab[l].cin_true = li.cin; tab[l].cin = b->ops[l].cin_pad; tab[l].cout = li.cout; tab[l].ksize = li.k;
+        }
+        DG_CUDA(cudaMalloc((void **)&b->pack_table, tab.size() * sizeof(PackLayer)));
+        DG_CUDA(cudaMemcpyAsync(b->pack_table, tab.data(), tab.size() * sizeof(PackLayer), cudaMemcpyHostToDevice, st));
+        DG_CUDA(cudaStreamSynchronize(st));
+    }
     DG_CUDA(cudaMalloc((void **)&b->scratch, scratch));
     b->scratch_bytes = scratch;
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
@@ -792,6 +845,7 @@ void dg_bf16_destroy(dg_model *m) {
     cudaFree(b->dz[0]); cudaFree(b->dz[1]); cudaFree(b->dz1);
     for (LayerOps &o : b->ops) { cudaFree(o.wf); if (o.wd) cudaFree(o.wd); cudaFree(o.ab); }
     cudaFree(b->scratch);
+    cudaFree(b->pack_table);
     delete b;
     m->bf = nullptr;
 }
@@ -799,15 +853,11 @@ void dg_bf16_destroy(dg_model *m) {
 int dg_bf16_params_changed(dg_model *m) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
-    for (int l = 0; l < m->L - 1; ++l) {
-        const LayerInfo &li = m->layers[l];
-        LayerOps &o = b->ops[l];
-        { dg_prof_scope _ps(c, DG_K_PACK);
-        pack_layer_kernel<<<b->num_sms * 2, 256, 0, c->stream>>>(m->params + li.offW, m->params + li.offB, m->params + li.offA, o.wf, o.wd, o.ab,
-                                                                 li.cin, o.cin_pad, li.cout, li.k, DG_R3, b->g3.pitch, b->g3.pad);
-                                                                 }
-        c->launches++;
+    {
+        dg_prof_scope _ps(c, DG_K_PACK);
+        pack_layer_kernel<<<dim3(b->num_sms, m->L - 1), 256, 0, c->stream>>>(b->pack_table, DG_R3, b->g3.pitch, b->g3.pad);
     }
+    c->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
 }
@@ -878,6 +928,7 @@ int dg_bf16_forward(dg_model *m) {
         if (int rc = launch_conv(m, cp)) return rc;
     }
     b->head_bwd_done = false;
+    if (m->fused_step) return 0;          // dg_train_step: the head runs once, in dg_bf16_backward
     return launch_head(m, false, 0.f);
 }
 
@@ -892,7 +943,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         const Geom &g = l == 0 ? b->g_first : b->g3;
         const bf16 *dzl = l == 0 ? b->dz1 : b->dz[cur];
         {
-            const int groups = 8;
+            const int groups = m->n >= 64 ? 32 : (m->n >= 8 ? 8 : 1);
             { dg_prof_scope _ps(c, DG_K_BIAS_GRAD);
             bias_grad_bf16_kernel<<<dim3(li.cout / 8, groups), 384, 0, c->stream>>>(dzl, m->grads + li.offA, m->grads + li.offB, m->n, li.cout,
                                                                                    g.rows, g.pitch, g.pad, groups);

@@ -14,6 +14,7 @@ struct dg_model {
     int n = 0;
     int global_batch = 0;
     bool have_targets = false, have_raw = false, forward_done = false;
+    bool fused_step = false;           // inside dg_train_step: forward and backward run back to back
     uint8_t *d_raw = nullptr, *d_player = nullptr, *d_rank = nullptr, *d_sym = nullptr, *d_x = nullptr, *d_y = nullptr;
     int32_t *d_targets = nullptr, *d_argmax = nullptr;
     float *d_logp = nullptr, *d_loss_n = nullptr, *d_loss = nullptr;
