@@ -47,6 +47,7 @@ extern "C" int dg_ctx_create(int device, dg_ctx **out) {
 
 extern "C" int dg_ctx_destroy(dg_ctx *c) {
     if (!c) return 0;
+    if (c->live_models > 0) { c->zombie = true; return 0; }   // a model still uses this context: free it with the last model
     cudaSetDevice(c->dev);
     cudaStreamSynchronize(c->stream);
     if (c->scratch) cudaFree(c->scratch);
@@ -217,6 +218,7 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
         m->layers.push_back(li);
     }
     m->P = off;
+    c->live_models++;
     const size_t B = max_batch;
     DG_CUDA(cudaMalloc(&m->params, m->P * 4));
     DG_CUDA(cudaMalloc(&m->grads, m->P * 4));
@@ -253,7 +255,9 @@ extern "C" int dg_model_destroy(dg_model *m) {
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
     cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
     cudaFree(m->d_loss); cudaFree(m->d_errors);
+    dg_ctx *c = m->ctx;
     delete m;
+    if (--c->live_models == 0 && c->zombie) { c->zombie = false; return dg_ctx_destroy(c); }
     return 0;
 }
 

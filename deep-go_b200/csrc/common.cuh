@@ -41,6 +41,8 @@ struct dg_prof_rec { int kind; cudaEvent_t e0, e1; };
 struct dg_ctx {
     int dev = 0;
     bool prof_on = false;
+    int live_models = 0;               // dg_ctx_destroy is deferred until the last model is gone
+    bool zombie = false;
     std::vector<dg_prof_rec> prof_recs;
     double prof_ms[DG_K_COUNT] = {0};
     long long prof_n[DG_K_COUNT] = {0};

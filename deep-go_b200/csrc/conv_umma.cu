@@ -13,6 +13,8 @@
 #include "model.cuh"
 #include "umma.cuh"
 #include "../../include/deepgo.h"
+#include <cstdio>
+#include <cstdlib>
 
 using namespace umma;
 typedef __nv_bfloat16 bf16;
@@ -46,12 +48,14 @@ struct ConvParams {
     int kp;               // channels per weight ring stage (multiple of 16); cin % kp == 0
     int nstages;
     int mode;
+    long long *dbg;       // optional per-CTA phase timestamps (DG_TIMELINE=1), 8 slots per CTA
 };
 
+#define DBG_STAMP(slot) do { if (p.dbg) p.dbg[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
 #define CONV_MAX_STAGES 8
 #define CONV_MAX_KPANELS 4
 
-__global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
+__global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES];
     __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_empty, acc_full, acc_empty;
@@ -69,11 +73,12 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
     const int chunks_kp = p.kp >> 3;
 
     if (threadIdx.x == 0) {
+        DBG_STAMP(0);
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
         for (int k = 0; k < nkp; ++k) mbar_init(&img_full[k], 1);
         mbar_init(&img_empty, 1);
         mbar_init(&acc_full, 1);
-        mbar_init(&acc_empty, 4);
+        mbar_init(&acc_empty, 8);
         fence_barrier_init();
     }
     if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
@@ -81,30 +86,38 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
+    if (threadIdx.x == 0) DBG_STAMP(1);
 
     if (warp == 0) {
-        // ===== producer: bulk copies of the position image and of the weight ring =====
-        if (lane == 0) {
-            uint32_t it = 0, j = 0;
-            for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
-                mbar_wait(&img_empty, (j & 1) ^ 1);
+        // ===== producer warp (converged; one elected lane issues the bulk copies) =====
+        // Stage / phase bookkeeping uses counters only: this warp and the MMA warp are single-issue scalar code,
+        // an integer division per stage costs more than the stage's MMAs.
+        uint32_t s = 0, ph = 0, j = 0;
+        const uint32_t panel_bytes = (uint32_t)chunks_kp * p.R_in * 16;
+        const size_t tap_stride = (size_t)chunks_in * p.cout * 16, kp_stride = (size_t)chunks_kp * p.cout * 16;
+        for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
+            mbar_wait(&img_empty, (j & 1) ^ 1);
+            if (elect_one()) {
                 const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
                 for (int k = 0; k < nkp; ++k) {
-                    mbar_arrive_expect_tx(&img_full[k], (uint32_t)chunks_kp * p.R_in * 16);
+                    mbar_arrive_expect_tx(&img_full[k], panel_bytes);
                     for (int c = 0; c < chunks_kp; ++c) {
                         const size_t off = (size_t)(k * chunks_kp + c) * p.R_in * 16;
                         bulk_g2s(img + off, src + off, (uint32_t)p.R_in * 16, &img_full[k]);
                     }
                 }
-                for (int nbk = 0; nbk < nnb; ++nbk)
-                    for (int k = 0; k < nkp; ++k)
-                        for (int t = 0; t < taps; ++t, ++it) {
-                            const int s = it % p.nstages;
-                            mbar_wait(&w_empty[s], ((it / p.nstages) & 1) ^ 1);
+            }
+            __syncwarp();
+            for (int nbk = 0; nbk < nnb; ++nbk) {
+                const uint8_t *w_k = (const uint8_t *)p.w + (size_t)nbk * p.nb * 16;
+                for (int k = 0; k < nkp; ++k, w_k += kp_stride) {
+                    const uint8_t *wsrc = w_k;
+                    for (int t = 0; t < taps; ++t, wsrc += tap_stride) {
+                        mbar_wait(&w_empty[s], ph ^ 1);
+                        if (elect_one()) {
                             mbar_arrive_expect_tx(&w_full[s], stage_bytes);
                             uint8_t *dst = ring + (size_t)s * stage_bytes;
                             // W[t][k*chunks_kp + c][nbk*nb .. +nb][8]
-                            const uint8_t *wsrc = (const uint8_t *)p.w + (((size_t)t * chunks_in + (size_t)k * chunks_kp) * p.cout + (size_t)nbk * p.nb) * 16;
                             if (nnb == 1) {
                                 bulk_g2s(dst, wsrc, stage_bytes, &w_full[s]);
                             } else {
@@ -112,117 +125,155 @@ __global__ void __launch_bounds__(192, 1) conv_umma_kernel(const ConvParams p) {
                                     bulk_g2s(dst + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
                             }
                         }
+                        __syncwarp();
+                        if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
+                    }
+                }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) =====
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(128, p.nb, 0, 0);
-            const uint32_t img_a = smem_u32(img), ring_a = smem_u32(ring);
-            const uint32_t a_lo0 = desc_lo(img_a, (uint32_t)p.R_in * 16), hi = desc_hi(128);
-            const uint32_t a_kstep = 2u * p.R_in, b_kstep = 2u * p.nb;
-            const int ksteps = p.kp >> 4;
-            uint32_t it = 0, j = 0, a = 0;
-            for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
-                for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                    mbar_wait(&acc_empty, (a & 1) ^ 1);
-                    tc_fence_after();
-                    for (int k = 0; k < nkp; ++k) {
-                        if (nbk == 0) mbar_wait(&img_full[k], j & 1);
-                        for (int t = 0; t < taps; ++t, ++it) {
-                            const int s = it % p.nstages;
-                            mbar_wait(&w_full[s], (it / p.nstages) & 1);
+        // ===== MMA warp (converged, so descriptors stay in uniform registers; one elected lane issues) =====
+        const uint32_t idesc = make_idesc_bf16(128, p.nb, 0, 0);
+        const uint32_t img_a = smem_u32(img), ring_a = smem_u32(ring);
+        const uint32_t hi = desc_hi(128);
+        const uint32_t a_lo_first = desc_lo(img_a, (uint32_t)p.R_in * 16) + (uint32_t)(p.first - p.pad_in * p.pitch_in - p.pad_in);
+        const uint32_t b_lo_ring = desc_lo(ring_a, (uint32_t)p.nb * 16);
+        const uint32_t a_kstep = 2u * p.R_in, b_kstep = 2u * p.nb, stage_units = stage_bytes >> 4;
+        const uint32_t a_panel = (uint32_t)chunks_kp * p.R_in;
+        const int ksteps = p.kp >> 4;
+        uint32_t s = 0, ph = 0, j = 0, a = 0;
+        uint32_t b_lo_s = b_lo_ring;
+        long long wait_cycles = 0;
+        for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
+            for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
+                mbar_wait(&acc_empty, (a & 1) ^ 1);
+                tc_fence_after();
+                uint32_t a_lo_k = a_lo_first;
+                uint32_t first_mma = 0;                           // 0 until the first MMA of this accumulator set has been issued
+                for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
+                    if (nbk == 0) { mbar_wait(&img_full[k], j & 1); if (j == 0 && lane == 0) DBG_STAMP(2 + (k > 0)); }
+                    uint32_t a_lo_ky = a_lo_k;                    // + ky*pitch + kx rows, in 16-byte units
+                    for (int ky = 0; ky < p.ksize; ++ky, a_lo_ky += p.pitch_in) {
+                        for (int kx = 0; kx < p.ksize; ++kx) {
+                            const long long tw0 = p.dbg ? clock64() : 0;
+                            mbar_wait(&w_full[s], ph);
+                            if (p.dbg) wait_cycles += clock64() - tw0;
                             tc_fence_after();
-                            const int ky = t / p.ksize, kx = t - ky * p.ksize;
-                            const int toff = (ky - p.pad_in) * p.pitch_in + (kx - p.pad_in);
-                            // descriptor low words in 16-byte units: +1 per image row, +R_in per channel chunk
-                            uint32_t a_tile = a_lo0 + (uint32_t)(k * chunks_kp) * p.R_in + (uint32_t)(p.first + toff);
-                            const uint32_t b_lo0 = desc_lo(ring_a + s * stage_bytes, (uint32_t)p.nb * 16);
-                            uint32_t d_tmem = tmem_base;
-                            const uint32_t acc0 = (k | t) != 0;
-                            for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
-                                uint32_t a_lo = a_tile, b_lo = b_lo0;
+                            if (elect_one()) {
+                                uint32_t a_tile = a_lo_ky + kx;
+                                uint32_t d_tmem = tmem_base;
+                                for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
+                                    uint32_t a_lo = a_tile, b_lo = b_lo_s;
 #pragma unroll 4
-                                for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep)
-                                    mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, acc0 | (uint32_t)ks);
+                                    for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep)
+                                        mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma | (uint32_t)ks);
+                                }
+                                mma_commit(&w_empty[s]);
                             }
-                            mma_commit(&w_empty[s]);
+                            __syncwarp();
+                            first_mma = 1;
+                            b_lo_s += stage_units;
+                            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; b_lo_s = b_lo_ring; }
                         }
                     }
-                    mma_commit(&acc_full);
                 }
-                mma_commit(&img_empty);
+                if (elect_one()) mma_commit(&acc_full);
+                __syncwarp();
+                if (a == 0 && lane == 0) { DBG_STAMP(4); if (p.dbg) p.dbg[blockIdx.x * 8 + 7] = wait_cycles; }
             }
+            if (elect_one()) mma_commit(&img_empty);
+            __syncwarp();
         }
     } else {
-        // ===== epilogue warps 2..5: TMEM -> registers -> bias/ReLU or mask -> bf16 -> HBM =====
-        const int q = warp & 3;                         // TMEM lane quarter this warp may access
+        // ===== epilogue warps 2..9: TMEM -> registers -> bias/ReLU or mask -> bf16 -> HBM =====
+        // warp w may only touch TMEM lanes 32*(w%4)..+31; two warps share a lane quarter and split the 32-column blocks.
+        const int q = warp & 3, half = (warp - 2) >> 2;
         const int chunks_out = p.cout >> 3;
+        const int nblk32 = p.nb >> 5;
+        const int my_blocks = (nblk32 - half + 1) >> 1;           // blocks half, half+2, ...
+        const int items = p.ntiles * my_blocks;
         uint32_t a = 0;
         for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x) {
             for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                mbar_wait(&acc_full, a & 1);
-                tc_fence_after();
-                for (int tile = 0; tile < p.ntiles; ++tile) {
+                // aux operand (bias or ReLU-mask source) of one item = 32 channels of one row: prefetched one item ahead
+                float4 bv[8];
+                uint4 mk[4];
+                auto row_of = [&](int item, int &rho_out, int &rho_m, bool &valid, int &tile, int &c0) {
+                    tile = item / my_blocks;
+                    c0 = ((item - tile * my_blocks) * 2 + half) * 32;
                     const int rho = p.first + tile * 128 + q * 32 + lane;
                     const int xp = rho / p.pitch_in, yp = rho - xp * p.pitch_in;
                     const int x = xp - p.pad_in, y = yp - p.pad_in;
-                    const bool valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
-                    const int rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
-                    const int rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
-                    for (int c0 = 0; c0 < p.nb; c0 += 32) {
-                        uint32_t r[32];
-                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
-                        const int chunk0 = (nbk * p.nb + c0) >> 3;
-                        float4 bv[8];
-                        uint4 mk[4];
-                        if (valid) {
+                    valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+                    rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
+                    rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
+                };
+                auto load_aux = [&](int item) {
+                    int rho_out, rho_m, tile, c0; bool valid;
+                    row_of(item, rho_out, rho_m, valid, tile, c0);
+                    if (!valid) return;
+                    const int chunk0 = (nbk * p.nb + c0) >> 3;
+                    if (p.mode == 0) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)(chunk0 + g) * p.R_out + rho_out) * 8);
+                            bv[2 * g] = __ldg(bp); bv[2 * g + 1] = __ldg(bp + 1);
+                        }
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+                            mk[g] = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
+                    }
+                };
+                if (items > 0) load_aux(0);               // in flight while the MMAs of this position finish
+                mbar_wait(&acc_full, a & 1);
+                tc_fence_after();
+                if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
+                for (int item = 0; item < items; ++item) {
+                    int rho_out, rho_m, tile, c0; bool valid;
+                    row_of(item, rho_out, rho_m, valid, tile, c0);
+                    const int chunk0 = (nbk * p.nb + c0) >> 3;
+                    uint32_t r[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+                    tmem_ld_wait();
+                    uint4 o[4];
+                    if (valid) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            float v[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
                             if (p.mode == 0) {
-#pragma unroll
-                                for (int g = 0; g < 4; ++g) {
-                                    const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)(chunk0 + g) * p.R_out + rho_out) * 8);
-                                    bv[2 * g] = __ldg(bp); bv[2 * g + 1] = __ldg(bp + 1);
-                                }
+                                const float4 b0 = bv[2 * g], b1 = bv[2 * g + 1];
+                                v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f);
+                                v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
+                                v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f);
+                                v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
                             } else {
+                                const uint32_t mw[4] = {mk[g].x, mk[g].y, mk[g].z, mk[g].w};
 #pragma unroll
-                                for (int g = 0; g < 4; ++g)
-                                    mk[g] = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
-                            }
-                        }
-                        tmem_ld_wait();
-                        if (valid) {
-#pragma unroll
-                            for (int g = 0; g < 4; ++g) {
-                                float v[8];
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
-                                if (p.mode == 0) {
-                                    const float4 b0 = bv[2 * g], b1 = bv[2 * g + 1];
-                                    v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f);
-                                    v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
-                                    v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f);
-                                    v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
-                                } else {
-                                    const uint32_t mw[4] = {mk[g].x, mk[g].y, mk[g].z, mk[g].w};
-#pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
-                                        // bf16 > 0  <=>  sign bit clear and not zero
-                                        if (!(h != 0 && (h & 0x8000u) == 0)) v[e] = 0.f;
-                                    }
+                                for (int e = 0; e < 8; ++e) {
+                                    const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                                    // bf16 > 0  <=>  sign bit clear and not zero
+                                    if (!(h != 0 && (h & 0x8000u) == 0)) v[e] = 0.f;
                                 }
-                                uint4 o;
-                                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-                                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
-                                o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
-                                o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
-                                *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk0 + g) * p.R_out + rho_out) * 8) = o;
                             }
+                            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+                            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
+                            o[g].x = *reinterpret_cast<uint32_t *>(&t0); o[g].y = *reinterpret_cast<uint32_t *>(&t1);
+                            o[g].z = *reinterpret_cast<uint32_t *>(&t2); o[g].w = *reinterpret_cast<uint32_t *>(&t3);
                         }
+                    }
+                    if (item + 1 < items) load_aux(item + 1);      // next item's aux loads overlap this item's stores
+                    if (valid) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+                            *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk0 + g) * p.R_out + rho_out) * 8) = o[g];
                     }
                 }
                 tc_fence_before();
                 __syncwarp();
+                if (a == 0 && threadIdx.x == 64) DBG_STAMP(6);
                 if (lane == 0) mbar_arrive(&acc_empty);
             }
         }
@@ -248,7 +299,7 @@ struct WgradParams {
     int nstages;
 };
 
-#define WG_RP 64          // K rows per stage
+#define WG_RP 128         // K rows per stage
 
 __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -282,46 +333,56 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
     const uint32_t tmem_base = tmem_base_s;
 
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int u = split; u < units; u += p.splits, ++it) {
-                const int pos = u / panels, panel = u - pos * panels;
-                const int s = it % p.nstages;
-                mbar_wait(&s_empty[s], ((it / p.nstages) & 1) ^ 1);
-                mbar_arrive_expect_tx(&s_full[s], (uint32_t)a_chunks * WG_RP * 16 + (uint32_t)(p.nb >> 3) * rb * 16);
+        uint32_t s = 0, ph = 0;
+        int pos = split / panels, panel = split - pos * panels;          // one division up front, counters afterwards
+        const int dpos = p.splits / panels, dpanel = p.splits - dpos * panels;
+        const int brow_off = (ky - p.pad) * p.pitch - p.pad;
+        const uint32_t tx = (uint32_t)a_chunks * WG_RP * 16 + (uint32_t)(p.nb >> 3) * rb * 16;
+        for (int u = split; u < units; u += p.splits) {
+            mbar_wait(&s_empty[s], ph ^ 1);
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&s_full[s], tx);
                 uint8_t *sa = smem + (size_t)s * stage_bytes, *sb = sa + a_bytes;
                 const int row0 = p.first + panel * WG_RP;
-                for (int c = 0; c < a_chunks; ++c)
-                    bulk_g2s(sa + (size_t)c * WG_RP * 16, (const uint8_t *)p.dz + (((size_t)pos * chunks_dz + mblk * 16 + c) * p.R + row0) * 16,
-                             WG_RP * 16, &s_full[s]);
-                const int brow0 = row0 + (ky - p.pad) * p.pitch - p.pad;
-                for (int c = 0; c < (p.nb >> 3); ++c)
-                    bulk_g2s(sb + (size_t)c * rb_pad * 16, (const uint8_t *)p.x + (((size_t)pos * chunks_x + nblk * (p.nb >> 3) + c) * p.R + brow0) * 16,
-                             (uint32_t)rb * 16, &s_full[s]);
+                const uint8_t *asrc = (const uint8_t *)p.dz + (((size_t)pos * chunks_dz + mblk * 16) * p.R + row0) * 16;
+                for (int c = 0; c < a_chunks; ++c, asrc += (size_t)p.R * 16)
+                    bulk_g2s(sa + (size_t)c * WG_RP * 16, asrc, WG_RP * 16, &s_full[s]);
+                const uint8_t *bsrc = (const uint8_t *)p.x + (((size_t)pos * chunks_x + nblk * (p.nb >> 3)) * p.R + row0 + brow_off) * 16;
+                for (int c = 0; c < (p.nb >> 3); ++c, bsrc += (size_t)p.R * 16)
+                    bulk_g2s(sb + (size_t)c * rb_pad * 16, bsrc, (uint32_t)rb * 16, &s_full[s]);
             }
+            __syncwarp();
+            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
+            pos += dpos; panel += dpanel;
+            if (panel >= panels) { panel -= panels; ++pos; }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(128, p.nb, 1, 1);
-            const uint32_t hi_a = desc_hi(WG_RP * 16), hi_b = desc_hi((uint32_t)rb_pad * 16);
-            uint32_t it = 0;
-            for (int u = split; u < units; u += p.splits, ++it) {
-                const int s = it % p.nstages;
-                mbar_wait(&s_full[s], (it / p.nstages) & 1);
-                tc_fence_after();
-                const uint32_t sa = smem_u32(smem) + s * stage_bytes, sb = sa + a_bytes;
-                const uint32_t a_lo0 = desc_lo(sa, 128), b_lo0 = desc_lo(sb, 128);
+        const uint32_t idesc = make_idesc_bf16(128, p.nb, 1, 1);
+        const uint32_t hi_a = desc_hi(WG_RP * 16), hi_b = desc_hi((uint32_t)rb_pad * 16);
+        const uint32_t a_lo_ring = desc_lo(smem_u32(smem), 128), b_lo_ring = desc_lo(smem_u32(smem) + a_bytes, 128);
+        const uint32_t stage_units = stage_bytes >> 4;
+        uint32_t s = 0, ph = 0, acc = 0;
+        uint32_t a_lo_s = a_lo_ring, b_lo_s = b_lo_ring;
+        for (int u = split; u < units; u += p.splits) {
+            mbar_wait(&s_full[s], ph);
+            tc_fence_after();
+            if (elect_one()) {
                 uint32_t d_tmem = tmem_base;
                 for (int kx = 0; kx < p.ksize; ++kx, d_tmem += p.nb) {
-                    uint32_t a_lo = a_lo0, b_lo = b_lo0 + kx;
+                    uint32_t a_lo = a_lo_s, b_lo = b_lo_s + kx;
 #pragma unroll
                     for (int ks = 0; ks < WG_RP / 16; ++ks, a_lo += 16, b_lo += 16)
-                        mma_bf16(d_tmem, desc_join(a_lo, hi_a), desc_join(b_lo, hi_b), idesc, it | (uint32_t)ks);
+                        mma_bf16(d_tmem, desc_join(a_lo, hi_a), desc_join(b_lo, hi_b), idesc, acc | (uint32_t)ks);
                 }
                 mma_commit(&s_empty[s]);
             }
-            mma_commit(&acc_full);
+            __syncwarp();
+            acc = 1;
+            a_lo_s += stage_units; b_lo_s += stage_units;
+            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; a_lo_s = a_lo_ring; b_lo_s = b_lo_ring; }
         }
+        if (elect_one()) mma_commit(&acc_full);
+        __syncwarp();
     } else {
         const int q = warp & 3;
         mbar_wait(&acc_full, 0);
@@ -734,7 +795,7 @@ static int conv_cfg(const dg_model *m, ConvParams &cp, int cin, int cout) {
     cp.cin = cin; cp.cout = cout;
     cp.nb = cout <= 128 ? cout : (cout % 96 == 0 ? 96 : (cout % 128 == 0 ? 128 : 64));
     DG_REQUIRE(cout % cp.nb == 0 && cp.nb % 16 == 0, "bf16 path: unsupported channel count %d", cout);
-    cp.kp = cin % 64 == 0 ? 64 : cin;
+    cp.kp = cin <= 128 ? cin : (cin % 64 == 0 ? 64 : cin);   // one ring stage = one tap x kp input channels
     DG_REQUIRE(cin % cp.kp == 0 && cp.kp % 16 == 0 && cin / cp.kp <= CONV_MAX_KPANELS, "bf16 path: unsupported input channel count %d", cin);
     DG_REQUIRE(cp.ntiles * cp.nb <= 512, "bf16 path: accumulator does not fit TMEM");
     return 0;
@@ -742,6 +803,10 @@ static int conv_cfg(const dg_model *m, ConvParams &cp, int cin, int cout) {
 
 static int launch_conv(dg_model *m, ConvParams cp) {
     dg_ctx *c = m->ctx;
+    static long long *dbg = nullptr;
+    static const bool timeline = getenv("DG_TIMELINE") != nullptr;
+    if (timeline && !dbg) cudaMalloc(&dbg, 148 * 8 * sizeof(long long));
+    cp.dbg = timeline ? dbg : nullptr;
     const size_t img_bytes = ((size_t)(cp.cin / 8) * cp.R_in * 16 + 1023) & ~(size_t)1023;
     const size_t stage = (size_t)cp.kp * cp.nb * 2;
     const size_t budget = 227 * 1024 - 1024;       // static smem (barriers) lives in the remaining KB
@@ -752,9 +817,20 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     const size_t smem = img_bytes + ns * stage;
     const int grid = cp.n < m->bf->num_sms ? cp.n : m->bf->num_sms;
     { dg_prof_scope _ps(c, cp.mode ? DG_K_DGRAD : (cp.ksize == 5 || cp.cin < cp.cout ? DG_K_CONV_FIRST : DG_K_CONV));
-    conv_umma_kernel<<<grid, 192, smem, c->stream>>>(cp);
+    conv_umma_kernel<<<grid, 320, smem, c->stream>>>(cp);
     }
     c->launches++;
+    if (timeline) {
+        std::vector<long long> h(148 * 8);
+        cudaStreamSynchronize(c->stream);
+        cudaMemcpy(h.data(), dbg, h.size() * 8, cudaMemcpyDeviceToHost);
+        double d[7] = {0};
+        for (int b = 0; b < grid; ++b) for (int i = 1; i < 7; ++i) d[i] += (double)(h[b * 8 + i] - h[b * 8]) / grid;
+        double w = 0;
+        for (int b = 0; b < grid; ++b) w += (double)h[b * 8 + 7] / grid;
+        fprintf(stderr, "conv timeline (cycles since CTA start, mean over %d CTAs) mode=%d k=%d: setup %.0f | img panel0 %.0f panel1 %.0f | mma issued %.0f | acc ready %.0f | epilogue done %.0f | weight-wait %.0f\n",
+                grid, cp.mode, cp.ksize, d[1], d[2], d[3], d[4], d[5], d[6], w);
+    }
     DG_CUDA(cudaGetLastError());
     return 0;
 }
@@ -781,8 +857,8 @@ static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const
 }
 
 int dg_bf16_create(dg_model *m) {
-    DG_REQUIRE(m->C % 16 == 0 && m->C >= 16 && m->C <= 256, "DG_PREC_BF16 needs channelSize %% 16 == 0 and <= 256 (got %d)", m->C);
-    DG_REQUIRE(384 % m->C == 0 || m->C > 384, "DG_PREC_BF16 head kernel needs channelSize dividing 384 (64, 96, 128, 192); got %d", m->C);
+    DG_REQUIRE(m->C % 32 == 0 && m->C >= 32 && m->C <= 256, "DG_PREC_BF16 needs channelSize %% 32 == 0 and <= 256 (got %d)", m->C);
+    DG_REQUIRE(384 % m->C == 0 || m->C > 384, "DG_PREC_BF16 head kernel needs channelSize dividing 384 (32, 64, 96, 128, 192); got %d", m->C);
     Bf16Path *b = new Bf16Path();
     m->bf = b;
     b->g_first = geom_for(m->k_first);
