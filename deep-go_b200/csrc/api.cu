@@ -391,6 +391,7 @@ static int backward_impl(dg_model *m) {
         const LayerInfo &li = m->layers[l];
         if (int rc = dg_simt_bias_grad(c, m->dz[cur], m->grads + li.offA, m->grads + li.offB, m->n, li.cout)) return rc;
         if (int rc = dg_simt_wgrad(c, m->act[l], m->dz[cur], m->grads + li.offW, m->n, li.cin, li.cout, li.k)) return rc;
+        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + li.offW, li.nW + li.cout + (size_t)li.cout * DG_POINTS)) return rc;
         if (l > 0) {
             // input gradient through the conv, then the ReLU mask of the layer below (h > 0 <=> z > 0)
             if (int rc = dg_simt_conv(c, m->dz[cur], m->params + li.offW, nullptr, nullptr, m->act[l], m->dz[cur ^ 1], m->n,
@@ -448,10 +449,17 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     if (!rc_f) rc_f = backward_impl(m);                                    // train.lua:8-10
     m->fused_step = false;
     if (rc_f) return rc_f;
-    if (c->world > 1) if (int rc = dg_dp_allreduce(c, m->grads, m->P)) return rc;
+    if (int rc = dg_dp_finish(c)) return rc;                               // buckets were issued layer by layer in backward
     if (int rc = dg_sgd_step(m, rate)) return rc;                          // train.lua:131
     if (loss_out) return read_loss(m, loss_out, nullptr);
     return 0;
+}
+
+extern "C" int dg_dp_allreduce_grads(dg_model *m) {
+    DG_REQUIRE(m, "dg_dp_allreduce_grads: model is NULL");
+    DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (int rc = dg_dp_bucket(m->ctx, m->grads, m->P)) return rc;
+    return dg_dp_finish(m->ctx);
 }
 
 extern "C" int dg_argmax(dg_model *m, int32_t *out) {

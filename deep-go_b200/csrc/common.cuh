@@ -108,4 +108,5 @@ int dg_launch_sgd(dg_ctx *ctx, float *p, const float *g, size_t n, float rate);
 int dg_launch_fill(dg_ctx *ctx, float *p, size_t n, float v);
 
 // ---- dp.cu
-int dg_dp_allreduce(dg_ctx *ctx, float *buf, size_t n);
+int dg_dp_bucket(dg_ctx *ctx, float *buf, size_t n);
+int dg_dp_finish(dg_ctx *ctx);

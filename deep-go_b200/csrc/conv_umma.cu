@@ -1012,6 +1012,10 @@ int dg_bf16_backward(dg_model *m, float scale) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
     if (int rc = launch_head(m, true, scale)) return rc;
+    {
+        const LayerInfo &lh = m->layers[m->L - 1];
+        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + lh.offW, lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS)) return rc;
+    }
     int cur = 0;                                           // dZ_{L-1} is in dz[0] (or dz1 when L-1 == 1)
     for (int l = m->L - 2; l >= 0; --l) {                  // conv layer index l (0-based) = layer l+1
         const LayerInfo &li = m->layers[l];
@@ -1044,6 +1048,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
                                                                        }
             c->launches++;
         }
+        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + li.offW, li.nW + li.cout + (size_t)li.cout * DG_POINTS)) return rc;
         if (l >= 1) {
             // dZ_{l} -> dZ_{l-1}: transposed conv with flipped taps, masked by ReLU of layer l's input h_l
             const bool into_first = (l - 1) == 0;

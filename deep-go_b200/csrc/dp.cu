@@ -56,13 +56,29 @@ extern "C" int dg_ctx_init_dp(dg_ctx *c, int rank, int world, const char id[128]
     memcpy(uid.internal, id, 128);
     int e = p_comm_init(&c->comm, world, uid, rank);
     DG_REQUIRE(e == 0, "ncclCommInitRank failed: %s", p_errstr(e));
+    DG_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+    DG_CUDA(cudaEventCreateWithFlags(&c->ev_grad_ready, cudaEventDisableTiming));
+    DG_CUDA(cudaEventCreateWithFlags(&c->ev_comm_done, cudaEventDisableTiming));
     return 0;
 }
 
-// in-place SUM over ranks on the context's stream (ncclFloat32 = 7, ncclSum = 0)
-int dg_dp_allreduce(dg_ctx *c, float *buf, size_t n) {
+// Gradient bucket exchange, overlapped with the rest of the backward pass: the bucket (one layer's W, b, a slice of
+// the flat gradient vector, contiguous in Torch7 order) is summed over ranks on the communication stream as soon as
+// the kernels that produce it have finished on the compute stream (ncclFloat32 = 7, ncclSum = 0).
+int dg_dp_bucket(dg_ctx *c, float *buf, size_t n) {
+    if (c->world <= 1 || n == 0) return 0;
     DG_REQUIRE(c->comm, "data parallel: dg_ctx_init_dp was not called");
-    int e = p_allreduce(buf, buf, n, 7, 0, c->comm, c->stream);
+    DG_CUDA(cudaEventRecord(c->ev_grad_ready, c->stream));
+    DG_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_grad_ready, 0));
+    int e = p_allreduce(buf, buf, n, 7, 0, c->comm, c->comm_stream);
     DG_REQUIRE(e == 0, "ncclAllReduce failed: %s", p_errstr(e));
+    c->launches++;
+    return 0;
+}
+// the compute stream continues (SGD) only after every bucket has been reduced
+int dg_dp_finish(dg_ctx *c) {
+    if (c->world <= 1) return 0;
+    DG_CUDA(cudaEventRecord(c->ev_comm_done, c->comm_stream));
+    DG_CUDA(cudaStreamWaitEvent(c->stream, c->ev_comm_done, 0));
     return 0;
 }

@@ -167,6 +167,9 @@ class Model:
         check(self.L.dg_loss_backward(self.h, loss))
         return float(loss[0])
 
+    def allreduce_grads(self):
+        check(self.L.dg_dp_allreduce_grads(self.h))
+
     def sgd_step(self, rate):
         check(self.L.dg_sgd_step(self.h, rate))
 

@@ -69,6 +69,9 @@ int dg_prof_get(dg_ctx *ctx, int kind, float *ms_total, long long *launches);
  * produce. */
 int dg_dp_unique_id(char id_out[128]);
 int dg_ctx_init_dp(dg_ctx *ctx, int rank, int world, const char id[128]);
+/* sum the whole gradient vector over ranks (for callers that run eval() and SGD:step as separate calls,
+ * train.lua:111 then :131); dg_train_step does this itself, bucket by bucket, overlapped with backward */
+int dg_dp_allreduce_grads(dg_model *m);
 
 /* ---- feature planes (dataloader.lua) ------------------------------------------------------ */
 /* preprocess() over a batch (dataloader.lua:50-92,113-121) with the D4 symmetry hook

@@ -1,0 +1,67 @@
+"""-m gpu, needs >= 2 GPUs (skipped otherwise): two ranks, one per GPU, train on the two halves of a batch through
+the library's bucketed NCCL allreduce and must end with the parameters of one rank training on the whole batch."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as entry
+
+pytestmark = pytest.mark.gpu
+
+WORKER = r'''
+import os, sys, numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["DG_ROOT"])
+from deepgo_b200.host import engine, dp
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+g = np.load(os.path.join(os.environ["DG_ROOT"], "tests", "golden", "positions.npz"))
+idx = np.arange(0, 160, 10); pl = g["player"][idx]
+batch = dict(raw=g["raw"][idx], player=pl, rank=g["ranks"][idx, pl - 1], x=g["x"][idx], y=g["y"][idx])
+flat = np.load(os.environ["DG_PARAMS"])
+ctx = engine.Context(rank)
+m = engine.Model(ctx, 4, 64, int(os.environ["DG_PREC"]), max_batch=16)
+dp.init_data_parallel(ctx, m, dist, rank, world, 16)
+m.set_params(flat)
+mine = dp.shard_batch(batch, rank, world)
+for _ in range(3):
+    m.set_batch_raw(mine["raw"], mine["player"], mine["rank"], None, mine["x"], mine["y"])
+    m.train_step(0.05)
+np.save(os.environ["DG_OUT"] + ".%d.npy" % rank, m.get_params())
+dist.barrier()
+dist.destroy_process_group()
+'''
+
+
+@pytest.mark.parametrize("prec", [0, 1])
+def test_two_gpus_match_one(tmp_path, prec):
+    entry.build()
+    from deepgo_b200.host import engine
+    if engine.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    g = np.load(os.path.join(entry.ROOT, "tests", "golden", "positions.npz"))
+    rng = np.random.default_rng(0)
+    ctx = engine.Context(0)
+    m = engine.Model(ctx, 4, 64, prec, max_batch=16)
+    flat = (rng.normal(0, 0.05, m.P)).astype(np.float32)
+    np.save(tmp_path / "p.npy", flat)
+    idx = np.arange(0, 160, 10); pl = g["player"][idx]
+    m.set_params(flat)
+    for _ in range(3):
+        m.set_batch_raw(g["raw"][idx], pl, g["ranks"][idx, pl - 1], None, g["x"][idx], g["y"][idx])
+        m.train_step(0.05)
+    ref = m.get_params()
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = tmp_path / "w.py"
+    script.write_text(WORKER)
+    env = dict(os.environ, DG_ROOT=entry.ROOT, DG_PARAMS=str(tmp_path / "p.npy"), DG_OUT=str(tmp_path / "out"), DG_PREC=str(prec))
+    subprocess.check_call([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                           "--master-port", str(port), str(script)], env=env, timeout=300)
+    a = np.load(str(tmp_path / "out") + ".0.npy"); b = np.load(str(tmp_path / "out") + ".1.npy")
+    assert np.array_equal(a, b)                          # replicas stay identical
+    tol = 1e-5 if prec == 0 else 2e-3
+    assert np.abs(a - ref).max() < tol
