@@ -224,13 +224,18 @@ def run_ours(args, rank, local_rank, world):
     h2d = BATCH * (9 * 361 + 5)
     assert np.isfinite(loss)
 
-    if rank != 0:
-        return
     # ---------------- per-kernel times for the roofline (a few extra steps, after the timed region) ----------------
+    # every rank runs them (the steps contain the gradient allreduce); rank 0 reports
     ctx.prof_begin()
     for _ in range(5):
         m.encode_resident(); m.train_step(rate, want_loss=False)
     prof = ctx.prof_end()
+    barrier()
+    if dist is not None and rank != 0:
+        dist.destroy_process_group()
+        return
+    if rank != 0:
+        return
     sustained, burst, hbm, peak_src = peaks()
     kern = {k: {"ms_per_step": v[0] / 5, "launches_per_step": v[1] / 5} for k, v in prof.items()}
     conv_ms, conv_n = prof.get("conv", (0.0, 0))
@@ -263,6 +268,8 @@ def run_ours(args, rank, local_rank, world):
         "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
         "tensor_frac_whole_step": {"achieved_tflops": whole, "of_sustained_peak": whole / sustained, "of_burst_peak": whole / burst},
         "kernels": kern}))
+    if dist is not None:
+        dist.destroy_process_group()
 
 
 def main():

@@ -21,11 +21,11 @@ def _deps_mtime():
 
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    srcs = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    srcs = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cpp")))
     hm = _deps_mtime()
     jobs = []
     for s in srcs:
-        src, obj = os.path.join(CSRC, s), os.path.join(OBJ, s[:-3] + ".o")
+        src, obj = os.path.join(CSRC, s), os.path.join(OBJ, os.path.splitext(s)[0] + ".o")
         if force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hm):
             jobs.append((src, obj))
 
@@ -41,7 +41,7 @@ def build(force=False, verbose=False):
     if verbose:
         for l in logs:
             sys.stderr.write(l)
-    objs = [os.path.join(OBJ, s[:-3] + ".o") for s in srcs]
+    objs = [os.path.join(OBJ, os.path.splitext(s)[0] + ".o") for s in srcs]
     if jobs or not os.path.exists(LIB):
         cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)

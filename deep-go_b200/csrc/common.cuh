@@ -72,16 +72,16 @@ int dg_ctx_scratch(dg_ctx *ctx, size_t bytes, void **out);
 
 // per-kernel CUDA-event timing (dg_prof_*): brackets one launch on the context's stream when enabled
 struct dg_prof_scope {
-    dg_ctx *c; int idx;
-    dg_prof_scope(dg_ctx *ctx, int kind) : c(ctx), idx(-1) {
+    dg_ctx *c; int idx; cudaStream_t st;
+    dg_prof_scope(dg_ctx *ctx, int kind, cudaStream_t stream = nullptr) : c(ctx), idx(-1), st(stream ? stream : ctx->stream) {
         if (!c->prof_on) return;
         dg_prof_rec r; r.kind = kind;
         cudaEventCreate(&r.e0); cudaEventCreate(&r.e1);
-        cudaEventRecord(r.e0, c->stream);
+        cudaEventRecord(r.e0, st);
         c->prof_recs.push_back(r);
         idx = (int)c->prof_recs.size() - 1;
     }
-    ~dg_prof_scope() { if (idx >= 0) cudaEventRecord(c->prof_recs[idx].e1, c->stream); }
+    ~dg_prof_scope() { if (idx >= 0) cudaEventRecord(c->prof_recs[idx].e1, st); }
 };
 
 // ---- encode.cu
@@ -108,5 +108,5 @@ int dg_launch_sgd(dg_ctx *ctx, float *p, const float *g, size_t n, float rate);
 int dg_launch_fill(dg_ctx *ctx, float *p, size_t n, float v);
 
 // ---- dp.cu
-int dg_dp_bucket(dg_ctx *ctx, float *buf, size_t n);
+int dg_dp_bucket(dg_ctx *ctx, float *buf, size_t n, cudaStream_t producer = nullptr);
 int dg_dp_finish(dg_ctx *ctx);

@@ -783,8 +783,12 @@ struct Bf16Path {
     bf16 *dz1 = nullptr;                   // dZ_1 in the first layer's geometry
     std::vector<LayerOps> ops;             // per conv layer 0..L-2
     PackLayer *pack_table = nullptr;       // device copy, one entry per conv layer
-    float *scratch = nullptr;              // weight-gradient partial tiles
-    size_t scratch_bytes = 0;
+    float *scratch = nullptr;              // weight-gradient partial tiles, two halves used alternately
+    size_t scratch_bytes = 0;              // bytes of one half
+    // the small HBM-bound gradient kernels (bias gradients, split-K reduction) run on a side stream, under the
+    // tensor-core kernels of the main stream
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_dz = nullptr, ev_wgrad = nullptr, ev_bias[2] = {nullptr, nullptr}, ev_reduce[2] = {nullptr, nullptr}, ev_join = nullptr;
     int num_sms = 148;
     bool head_bwd_done = false;
 };
@@ -905,8 +909,11 @@ int dg_bf16_create(dg_model *m) {
         DG_CUDA(cudaMemcpyAsync(b->pack_table, tab.data(), tab.size() * sizeof(PackLayer), cudaMemcpyHostToDevice, st));
         DG_CUDA(cudaStreamSynchronize(st));
     }
-    DG_CUDA(cudaMalloc((void **)&b->scratch, scratch));
+    DG_CUDA(cudaMalloc((void **)&b->scratch, 2 * scratch));
     b->scratch_bytes = scratch;
+    DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
+    cudaEvent_t *evs[] = {&b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
+    for (cudaEvent_t *e : evs) DG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
     DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
     DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
@@ -922,6 +929,7 @@ void dg_bf16_destroy(dg_model *m) {
     for (LayerOps &o : b->ops) { cudaFree(o.wf); if (o.wd) cudaFree(o.wd); cudaFree(o.ab); }
     cudaFree(b->scratch);
     cudaFree(b->pack_table);
+    if (b->side) cudaStreamDestroy(b->side);
     delete b;
     m->bf = nullptr;
 }
@@ -1022,33 +1030,46 @@ int dg_bf16_backward(dg_model *m, float scale) {
         const LayerOps &o = b->ops[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
         const bf16 *dzl = l == 0 ? b->dz1 : b->dz[cur];
+        const int par = l & 1;
+        float *scratch = b->scratch + (size_t)par * (b->scratch_bytes / 4);
+        // dZ_l is complete on the main stream: the side stream may read it
+        DG_CUDA(cudaEventRecord(b->ev_dz, c->stream));
+        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
         {
             const int groups = m->n >= 64 ? 32 : (m->n >= 8 ? 8 : 1);
-            { dg_prof_scope _ps(c, DG_K_BIAS_GRAD);
-            bias_grad_bf16_kernel<<<dim3(li.cout / 8, groups), 384, 0, c->stream>>>(dzl, m->grads + li.offA, m->grads + li.offB, m->n, li.cout,
-                                                                                   g.rows, g.pitch, g.pad, groups);
-                                                                                   }
+            dg_prof_scope _ps(c, DG_K_BIAS_GRAD, b->side);
+            bias_grad_bf16_kernel<<<dim3(li.cout / 8, groups), 384, 0, b->side>>>(dzl, m->grads + li.offA, m->grads + li.offB, m->n, li.cout,
+                                                                                 g.rows, g.pitch, g.pad, groups);
             c->launches++;
         }
+        DG_CUDA(cudaEventRecord(b->ev_bias[par], b->side));
         {
             WgradPlan w;
             if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
             WgradParams wp{};
-            wp.dz = dzl; wp.x = l == 0 ? b->x0 : b->h[l]; wp.scratch = b->scratch;
+            wp.dz = dzl; wp.x = l == 0 ? b->x0 : b->h[l]; wp.scratch = scratch;
             wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
             wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
             wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
+            // this scratch half was last read by the reduction two layers ago
+            DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
             { dg_prof_scope _ps(c, DG_K_WGRAD);
             wgrad_umma_kernel<<<w.combos * w.splits, 192, w.smem, c->stream>>>(wp);
             }
             c->launches++;
-            { dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE);
-            wgrad_reduce_kernel<<<b->num_sms * 4, 256, 0, c->stream>>>(b->scratch, m->grads + li.offW, li.cin, o.cin_pad, li.cout, li.k, w.nb,
-                                                                       w.n_mblk, w.n_nblk, w.splits);
-                                                                       }
+            DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
+            DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));
+            { dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
+            wgrad_reduce_kernel<<<b->num_sms * 4, 256, 0, b->side>>>(scratch, m->grads + li.offW, li.cin, o.cin_pad, li.cout, li.k, w.nb,
+                                                                     w.n_mblk, w.n_nblk, w.splits);
+            }
             c->launches++;
+            DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
         }
-        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + li.offW, li.nW + li.cout + (size_t)li.cout * DG_POINTS)) return rc;
+        // the layer's gradient slice is final once the side stream has run both kernels
+        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + li.offW, li.nW + li.cout + (size_t)li.cout * DG_POINTS, b->side)) return rc;
+        // the next dgrad overwrites the dZ buffer that the bias-gradient kernel of the layer above was reading
+        DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_bias[par ^ 1], 0));
         if (l >= 1) {
             // dZ_{l} -> dZ_{l-1}: transposed conv with flipped taps, masked by ReLU of layer l's input h_l
             const bool into_first = (l - 1) == 0;
@@ -1065,6 +1086,8 @@ int dg_bf16_backward(dg_model *m, float scale) {
             cur ^= 1;
         }
     }
+    DG_CUDA(cudaEventRecord(b->ev_join, b->side));
+    DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_join, 0));
     DG_CUDA(cudaGetLastError());
     return 0;
 }

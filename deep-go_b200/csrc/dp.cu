@@ -65,10 +65,10 @@ extern "C" int dg_ctx_init_dp(dg_ctx *c, int rank, int world, const char id[128]
 // Gradient bucket exchange, overlapped with the rest of the backward pass: the bucket (one layer's W, b, a slice of
 // the flat gradient vector, contiguous in Torch7 order) is summed over ranks on the communication stream as soon as
 // the kernels that produce it have finished on the compute stream (ncclFloat32 = 7, ncclSum = 0).
-int dg_dp_bucket(dg_ctx *c, float *buf, size_t n) {
+int dg_dp_bucket(dg_ctx *c, float *buf, size_t n, cudaStream_t producer) {
     if (c->world <= 1 || n == 0) return 0;
     DG_REQUIRE(c->comm, "data parallel: dg_ctx_init_dp was not called");
-    DG_CUDA(cudaEventRecord(c->ev_grad_ready, c->stream));
+    DG_CUDA(cudaEventRecord(c->ev_grad_ready, producer ? producer : c->stream));
     DG_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_grad_ready, 0));
     int e = p_allreduce(buf, buf, n, 7, 0, c->comm, c->comm_stream);
     DG_REQUIRE(e == 0, "ncclAllReduce failed: %s", p_errstr(e));

@@ -1,0 +1,51 @@
+-- data.lua of deep-go, re-hosted: Dataset index (<root>/<dir>_game_counts.txt), random (game, move) sampling and
+-- the queue_on_minibatch / do_queued_tasks pair (data.lua:29-37,53-96).  Without the `threads` rock the jobs run
+-- inline when the queue is drained; callbacks still run on the main Lua state, as in the reference.
+require 'dataloader'
+
+Dataset = {}
+Dataset.root = "/home/ubuntu/ebs_disk"
+Dataset.directory = "train"
+
+local queued = {}
+
+function Dataset:new(dict)
+    local result = {}
+    for k, v in pairs(self) do result[k] = v end
+    for k, v in pairs(dict or {}) do result[k] = v end
+    self.__index = self
+    return setmetatable(result, self)
+end
+
+function Dataset:init()
+    self.games = {}
+    local file = self.root .. "/" .. self.directory .. "_game_counts.txt"
+    local counts = assert(io.open(file), "unable to find counts (probably bad dataset path)")
+    for line in counts:lines() do
+        local name, size = line:match("^(.-)\t%s*(%d+)%s*$")
+        size = tonumber(size)
+        if name and size > 0 then table.insert(self.games, {name = name, size = size}) end   -- empty games dropped
+    end
+    counts:close()
+    self.initialized = true
+end
+
+function Dataset:generate_random_filename()
+    if not self.initialized then self:init() end
+    local game = self.games[math.random(1, #self.games)]
+    return game.name .. "/" .. math.random(1, game.size)
+end
+
+function queue_on_minibatch(f, dataset, n)
+    if dataset.initialized ~= true then dataset:init() end
+    local filenames = {}
+    for i = 1, n do filenames[i] = dataset:generate_random_filename() end
+    table.insert(queued, {filenames = filenames, callback = f})
+end
+
+function do_queued_tasks()
+    while #queued > 0 do
+        local job = table.remove(queued, 1)
+        job.callback(load_minibatch(job.filenames))
+    end
+end

@@ -89,6 +89,10 @@ int dg_encode(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint
  * records, result 0-based.  Pure host helper, reentrant. */
 int dg_encode_labels(const uint8_t *x, const uint8_t *y, const uint8_t *sym, int n, int32_t *out);
 
+/* torch.load of one position record (dataloader.lua:123-125) without Torch7: fills raw u8[9*19*19] and the
+ * 1-based move / player / ranks exactly as stored.  Host-only, reentrant (loader threads, data.lua:14-19). */
+int dg_t7_read_record(const char *path, uint8_t *raw, int *x, int *y, int *player, int ranks[2]);
+
 /* ---- board analysis (makedata.lua) --------------------------------------------------------- */
 /* summarize_board (makedata.lua:143-153): stones u8[n][19][19] in {0,1,2} ->
  * out u8[n][7][19][19]: liberties, liberties_after[p=1,2], kills[p=1,2], ladders[p=1,2]. */

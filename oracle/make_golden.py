@@ -37,6 +37,17 @@ def main():
         player=np.array(ps, np.uint8), ranks=np.array(rks, np.uint8), game=np.array(gi, np.int32),
         move=np.array(mi, np.int32), split=np.array(sp, np.uint8), games=np.array(games))
     print("wrote", OUT, len(raws), "records", os.path.getsize(OUT), "bytes")
+    # a handful of records in their original Torch7 wire format (3,598 B each) for the record-reader tests,
+    # laid out like the reference's data/ tree with its index file (data.lua:53-80)
+    import shutil
+    rec_root = os.path.join(os.path.dirname(OUT), "records")
+    game = "data/test/1993/2000-03-24b.sgf"
+    os.makedirs(os.path.join(rec_root, game), exist_ok=True)
+    for m in (1, 2, 3, 60, 125):
+        shutil.copyfile(os.path.join(REF, game, str(m)), os.path.join(rec_root, game, str(m)))
+    with open(os.path.join(rec_root, "data", "test_game_counts.txt"), "w") as f:
+        f.write("%s\t%8d\n" % (game, 3))          # moves 1..3 are present consecutively
+        f.write("data/test/1993/empty.sgf\t%8d\n" % 0)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,109 @@
+"""Host mirror of the reference's Lua modules (deep-go_b200/host): CPU-side checks here, the localtest.lua replay
+and loader parity under -m gpu."""
+import os
+import shutil
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as entry
+
+REC = os.path.join(entry.ROOT, "tests", "golden", "records")
+GAME = "data/test/1993/2000-03-24b.sgf"
+
+
+@pytest.fixture(scope="module")
+def host():
+    entry.build()
+    from deepgo_b200.host import dataloader, data, optimizer, experiments, train, engine
+    return dict(dataloader=dataloader, data=data, optimizer=optimizer, experiments=experiments, train=train, engine=engine)
+
+
+def test_channel_constants_match_reference(host):
+    d = host["dataloader"]        # dataloader.lua:6-27
+    assert (d.STONE, d.LIBERTIES, d.LIBERTIES_AFTER, d.KILL, d.AGE, d.LADDER, d.RANK, d.TOTAL, d.SIZE) == (1, 4, 8, 15, 22, 27, 28, 37, 19)
+    assert (d.INPUT.stone, d.INPUT.liberties, d.INPUT.liberties_after, d.INPUT.kills, d.INPUT.age, d.INPUT.ladder, d.INPUT.total) == (1, 2, 3, 5, 7, 8, 9)
+    assert d.input_dimensions == [37, 19, 19]
+
+
+def test_record_reader_matches_packed_corpus(host, golden):
+    d = host["dataloader"]
+    sel = np.where(golden["split"] == 2)[0]
+    for mv in (1, 2, 3, 60, 125):
+        i = sel[golden["move"][sel] == mv][0]
+        r = d.read_record(os.path.join(REC, GAME, str(mv)))
+        assert np.array_equal(r["input"], golden["raw"][i])
+        assert (r["move"]["x"], r["move"]["y"], r["move"]["player"]) == (golden["x"][i], golden["y"][i], golden["player"][i])
+        assert (r["ranks"][1], r["ranks"][2]) == tuple(golden["ranks"][i])
+    import deepgo_b200
+    with pytest.raises(deepgo_b200.DeepGoError):
+        d.read_record(os.path.join(REC, "nope"))
+    with pytest.raises(deepgo_b200.DeepGoError):          # not a Torch7 file
+        d.read_record(os.path.join(REC, "data", "test_game_counts.txt"))
+
+
+def test_dataset_index(host):
+    ds = host["data"].Dataset(root=os.path.join(REC, "data"), directory="test")
+    ds.init()
+    assert ds.games == [{"name": GAME, "size": 3}]        # the zero-move game is dropped (data.lua:74)
+    for _ in range(20):
+        name = ds.generate_random_filename()
+        assert name.startswith(GAME + "/") and 1 <= int(name.rsplit("/", 1)[1]) <= 3
+    with pytest.raises(IOError):
+        host["data"].Dataset(root=REC, directory="missing").init()
+
+
+def test_flatten_data_layout(host):
+    d = host["dataloader"]
+    z = np.zeros((19, 19), np.uint8)
+    rec = d.flatten_data(dict(stones=z + 1, liberties=z + 2, liberties_after=np.stack([z + 3, z + 4]), kills=np.stack([z + 5, z + 6]),
+                              age=z + 7, ladders=np.stack([z + 8, z + 9]), move={"x": 1, "y": 2, "player": 1}, ranks={1: 3, 2: 4}))
+    assert [int(rec["input"][i, 0, 0]) for i in range(9)] == [1, 2, 3, 4, 5, 6, 7, 8, 9] and rec["flat"]
+
+
+def _make_tree(tmp_path):
+    """a data_root with train/validation/test index files over the 3 consecutive fixture records"""
+    root = tmp_path / "root"
+    shutil.copytree(os.path.join(REC, "data"), root / "data")
+    for split in ("train", "validation"):
+        shutil.copyfile(root / "data" / "test_game_counts.txt", root / "data" / (split + "_game_counts.txt"))
+    return root
+
+
+@pytest.mark.gpu
+def test_load_minibatch_matches_oracle(host, golden):
+    from oracle import encode
+    files = [os.path.join(REC, GAME, str(m)) for m in (1, 2, 3, 60, 125)]
+    mb = host["dataloader"].load_minibatch(files)
+    assert mb["input"].shape == (5, 37, 19, 19) and mb["output"].shape == (5,)
+    for k, r in enumerate(mb["records"]):
+        pl = r["move"]["player"]
+        ref = encode.preprocess(r["input"], pl, r["ranks"][pl])
+        assert np.array_equal(mb["input"][k], ref.astype(np.float32))
+        assert mb["output"][k] == 19 * (r["move"]["x"] - 1) + r["move"]["y"]          # 1-based, dataloader.lua:89
+    one = host["dataloader"].load_and_preprocess(files[3])
+    assert np.array_equal(one["input"], mb["input"][3]) and one["output"] == mb["output"][3]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", [0, 1])
+def test_localtest_replay(host, tmp_path, capsys, precision):
+    """localtest.lua: basicGoExperiment (3 layers x 64), batchSize 2, validation_interval 20, iters 20."""
+    ex = host["experiments"]
+    root = _make_tree(tmp_path)
+    e = ex.basicGoExperiment.new(dict(useCuda=False, data_root=str(root / "data"), validation_interval=20, validationSize=4, batchSize=2,
+                                      precision=precision, rate=0.05))
+    os.chdir(tmp_path)
+    e.init()
+    rng = np.random.default_rng(0)
+    e.modelParameters.copy(rng.normal(0, 0.03, e.model.engine.P).astype(np.float32))
+    costs, vcosts = e.run({"iters": 20, "base": str(root)})
+    out = capsys.readouterr().out
+    assert "validation at iteration 20" in out and "training" in out and "total samples per second" in out
+    assert e.iterations == 20 and len(costs) == 2 and len(vcosts) == 1
+    assert np.isfinite(costs).all() and costs[-1] < np.log(361)          # 3 positions are memorised quickly
+    assert abs(e.optimizer.rate - 0.05 * (1 - 1e-7) ** 20) < 1e-12       # optimizer.lua:26
+    # checkpoint / resume in the flat parameter layout (experiments.lua:124-131)
+    fn = e.save(str(tmp_path / "ck.model"))
+    e2 = ex.Experiment.load(fn)
+    assert e2.iterations == 20 and np.array_equal(e2.modelParameters.numpy(), e.modelParameters.numpy())
