@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 
 static thread_local char g_err[1024] = "";
 
@@ -233,6 +234,8 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     DG_CUDA(cudaMalloc(&m->d_loss_n, B * 4));
     DG_CUDA(cudaMalloc(&m->d_loss, 4));
     DG_CUDA(cudaMalloc(&m->d_errors, 4));
+    DG_CUDA(cudaMalloc(&m->d_rate, 4));
+    DG_CUDA(cudaMallocHost(&m->h_rate, 4));
     m->act.assign(num_layers + 1, nullptr);
     DG_CUDA(cudaMalloc(&m->act[0], B * in_planes * DG_POINTS * 4));
     if (precision == DG_PREC_FP32) {
@@ -254,7 +257,8 @@ extern "C" int dg_model_destroy(dg_model *m) {
     for (int i = 0; i < 2; ++i) if (m->dz[i]) cudaFree(m->dz[i]);
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
     cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
-    cudaFree(m->d_loss); cudaFree(m->d_errors);
+    cudaFree(m->d_loss); cudaFree(m->d_errors); cudaFree(m->d_rate); cudaFreeHost(m->h_rate);
+    if (m->step_graph) cudaGraphExecDestroy(m->step_graph);
     dg_ctx *c = m->ctx;
     delete m;
     if (--c->live_models == 0 && c->zombie) { c->zombie = false; return dg_ctx_destroy(c); }
@@ -438,19 +442,57 @@ extern "C" int dg_sgd_step(dg_model *m, float rate) {
     return 0;
 }
 
+// one fused step on the context's stream: eval() of train.lua:4-12 followed by SGD:step (train.lua:131)
+static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
+    dg_ctx *c = m->ctx;
+    DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));          // train.lua:5
+    m->fused_step = true;
+    int rc = forward_impl(m);                                              // train.lua:6
+    if (!rc) rc = backward_impl(m);                                        // train.lua:8-10
+    m->fused_step = false;
+    if (rc) return rc;
+    if (int rc2 = dg_dp_finish(c)) return rc2;                             // buckets were issued layer by layer in backward
+    if (rate_from_device) {
+        if (int rc2 = dg_launch_sgd_dev_rate(c, m->params, m->grads, m->P, m->d_rate)) return rc2;
+        return dg_bf16_params_changed(m);
+    }
+    return dg_sgd_step(m, rate);                                           // train.lua:131
+}
+
 extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     DG_REQUIRE(m, "dg_train_step: model is NULL");
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
     DG_REQUIRE(m->have_targets, "dg_train_step: the staged batch has no targets");
-    DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));          // train.lua:5
-    m->fused_step = true;
-    int rc_f = forward_impl(m);                                            // train.lua:6
-    if (!rc_f) rc_f = backward_impl(m);                                    // train.lua:8-10
-    m->fused_step = false;
-    if (rc_f) return rc_f;
-    if (int rc = dg_dp_finish(c)) return rc;                               // buckets were issued layer by layer in backward
-    if (int rc = dg_sgd_step(m, rate)) return rc;                          // train.lua:131
+    DG_REQUIRE(m->n > 0, "dg_train_step: no batch staged");
+    static const bool no_graph = getenv("DG_NO_GRAPH") != nullptr || getenv("DG_TIMELINE") != nullptr;
+    const bool use_graph = m->prec == DG_PREC_BF16 && c->world == 1 && !c->prof_on && !no_graph;
+    if (use_graph) {
+        // the ~50 launches and the cross-stream event edges of a step are captured once per batch size and replayed
+        *m->h_rate = rate;
+        DG_CUDA(cudaMemcpyAsync(m->d_rate, m->h_rate, 4, cudaMemcpyHostToDevice, c->stream));
+        if (!m->step_graph || m->step_graph_n != m->n) {
+            if (m->step_graph) { cudaGraphExecDestroy(m->step_graph); m->step_graph = nullptr; }
+            const long long l0 = c->launches;
+            cudaGraph_t graph = nullptr;
+            DG_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+            const int rc = train_step_body(m, rate, true);
+            cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+            if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+            DG_REQUIRE(e == cudaSuccess && graph, "dg_train_step: graph capture failed: %s", cudaGetErrorString(e));
+            e = cudaGraphInstantiate(&m->step_graph, graph, 0);
+            cudaGraphDestroy(graph);
+            DG_REQUIRE(e == cudaSuccess, "dg_train_step: cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
+            m->step_graph_n = m->n;
+            m->step_graph_launches = c->launches - l0;
+            c->launches = l0;
+        }
+        DG_CUDA(cudaGraphLaunch(m->step_graph, c->stream));
+        c->launches += m->step_graph_launches;
+        m->forward_done = true;
+    } else {
+        if (int rc = train_step_body(m, rate, false)) return rc;
+    }
     if (loss_out) return read_loss(m, loss_out, nullptr);
     return 0;
 }

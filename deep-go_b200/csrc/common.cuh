@@ -70,6 +70,23 @@ struct LayerInfo {
 
 int dg_ctx_scratch(dg_ctx *ctx, size_t bytes, void **out);
 
+// Programmatic dependent launch: the kernel may be scheduled while its predecessor in the stream is still running;
+// it must execute dg_pdl_wait() before touching global memory (all kernels of the step do, so completion is transitive).
+#ifdef __CUDACC__
+__device__ __forceinline__ void dg_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void dg_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+static inline cudaError_t dg_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 // per-kernel CUDA-event timing (dg_prof_*): brackets one launch on the context's stream when enabled
 struct dg_prof_scope {
     dg_ctx *c; int idx; cudaStream_t st;
@@ -105,6 +122,7 @@ int dg_launch_loss_reduce(dg_ctx *ctx, const float *loss_n, const int32_t *argma
 
 // ---- sgd.cu
 int dg_launch_sgd(dg_ctx *ctx, float *p, const float *g, size_t n, float rate);
+int dg_launch_sgd_dev_rate(dg_ctx *ctx, float *p, const float *g, size_t n, const float *rate_dev);
 int dg_launch_fill(dg_ctx *ctx, float *p, size_t n, float v);
 
 // ---- dp.cu

@@ -15,6 +15,7 @@
 #include "../../include/deepgo.h"
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 
 using namespace umma;
 typedef __nv_bfloat16 bf16;
@@ -52,13 +53,14 @@ struct ConvParams {
 };
 
 #define DBG_STAMP(slot) do { if (p.dbg) p.dbg[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
+__device__ __forceinline__ long long dg_globaltimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define CONV_MAX_STAGES 8
 #define CONV_MAX_KPANELS 4
 
 __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES];
-    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_empty, acc_full, acc_empty;
+    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_empty, acc_full, acc_ready;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -72,13 +74,14 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
     const int nnb = p.cout / p.nb;
     const int chunks_kp = p.kp >> 3;
 
+    dg_pdl_launch_dependents();
     if (threadIdx.x == 0) {
         DBG_STAMP(0);
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
         for (int k = 0; k < nkp; ++k) mbar_init(&img_full[k], 1);
         mbar_init(&img_empty, 1);
         mbar_init(&acc_full, 1);
-        mbar_init(&acc_empty, 8);
+        mbar_init(&acc_ready, 8);
         fence_barrier_init();
     }
     if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
@@ -86,7 +89,8 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
-    if (threadIdx.x == 0) DBG_STAMP(1);
+    dg_pdl_wait();                 // everything above overlapped the previous kernel's tail; its output is visible from here on
+    if (threadIdx.x == 0) { DBG_STAMP(1); if (p.dbg) p.dbg[148 * 8 + blockIdx.x * 2] = dg_globaltimer(); }
 
     if (warp == 0) {
         // ===== producer warp (converged; one elected lane issues the bulk copies) =====
@@ -146,10 +150,12 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
         long long wait_cycles = 0;
         for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
             for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                mbar_wait(&acc_empty, (a & 1) ^ 1);
+                // the epilogue warps have drained the previous accumulators and, in forward mode, pre-loaded the new ones
+                // with the bias, so every forward MMA accumulates
+                mbar_wait(&acc_ready, a & 1);
                 tc_fence_after();
                 uint32_t a_lo_k = a_lo_first;
-                uint32_t first_mma = 0;                           // 0 until the first MMA of this accumulator set has been issued
+                uint32_t first_mma = p.mode == 0 ? 1u : 0u;       // 0 until the first MMA of this accumulator set has been issued
                 for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
                     if (nbk == 0) { mbar_wait(&img_full[k], j & 1); if (j == 0 && lane == 0) DBG_STAMP(2 + (k > 0)); }
                     uint32_t a_lo_ky = a_lo_k;                    // + ky*pitch + kx rows, in 16-byte units
@@ -195,9 +201,6 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
         uint32_t a = 0;
         for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x) {
             for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                // aux operand (bias or ReLU-mask source) of one item = 32 channels of one row: prefetched one item ahead
-                float4 bv[8];
-                uint4 mk[4];
                 auto row_of = [&](int item, int &rho_out, int &rho_m, bool &valid, int &tile, int &c0) {
                     tile = item / my_blocks;
                     c0 = ((item - tile * my_blocks) * 2 + half) * 32;
@@ -208,79 +211,103 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
                     rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
                     rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
                 };
-                auto load_aux = [&](int item) {
-                    int rho_out, rho_m, tile, c0; bool valid;
-                    row_of(item, rho_out, rho_m, valid, tile, c0);
-                    if (!valid) return;
-                    const int chunk0 = (nbk * p.nb + c0) >> 3;
-                    if (p.mode == 0) {
+                // ---- before the MMAs: no global load is left for the drain below.
+                // forward: the accumulators start as bias[c] + a[c][x][y] (written to TMEM while the image is still landing);
+                // backward: the ReLU mask of each item is compressed to one 32-bit word while the MMAs run.
+                uint32_t masks[8];
+                if (p.mode == 0) {
+                    for (int item = 0; item < items; ++item) {
+                        int rho_out, rho_m, tile, c0; bool valid;
+                        row_of(item, rho_out, rho_m, valid, tile, c0);
+                        const int chunk0 = (nbk * p.nb + c0) >> 3;
+                        uint32_t r[32];
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
-                            const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)(chunk0 + g) * p.R_out + rho_out) * 8);
-                            bv[2 * g] = __ldg(bp); bv[2 * g + 1] = __ldg(bp + 1);
+                            float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+                            if (valid) {
+                                const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)(chunk0 + g) * p.R_out + rho_out) * 8);
+                                b0 = __ldg(bp); b1 = __ldg(bp + 1);
+                            }
+                            r[g * 8 + 0] = __float_as_uint(b0.x); r[g * 8 + 1] = __float_as_uint(b0.y);
+                            r[g * 8 + 2] = __float_as_uint(b0.z); r[g * 8 + 3] = __float_as_uint(b0.w);
+                            r[g * 8 + 4] = __float_as_uint(b1.x); r[g * 8 + 5] = __float_as_uint(b1.y);
+                            r[g * 8 + 6] = __float_as_uint(b1.z); r[g * 8 + 7] = __float_as_uint(b1.w);
                         }
-                    } else {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g)
-                            mk[g] = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
+                        tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
                     }
-                };
-                if (items > 0) load_aux(0);               // in flight while the MMAs of this position finish
+                    tmem_st_wait();
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_ready);
+                if (p.mode != 0) {
+#pragma unroll
+                    for (int item = 0; item < 8; ++item) {
+                        masks[item] = 0;
+                        if (item < items) {
+                            int rho_out, rho_m, tile, c0; bool valid;
+                            row_of(item, rho_out, rho_m, valid, tile, c0);
+                            if (valid) {
+                                const int chunk0 = (nbk * p.nb + c0) >> 3;
+                                uint32_t mbits = 0;
+#pragma unroll
+                                for (int g = 0; g < 4; ++g) {
+                                    const uint4 mk = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
+                                    const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e) {
+                                        const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                                        // bf16 > 0  <=>  sign bit clear and not zero
+                                        if (h != 0 && (h & 0x8000u) == 0) mbits |= 1u << (g * 8 + e);
+                                    }
+                                }
+                                masks[item] = mbits;
+                            }
+                        }
+                    }
+                }
                 mbar_wait(&acc_full, a & 1);
                 tc_fence_after();
                 if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
-                for (int item = 0; item < items; ++item) {
+#pragma unroll
+                for (int item = 0; item < 8; ++item) {
+                    if (item >= items) break;
                     int rho_out, rho_m, tile, c0; bool valid;
                     row_of(item, rho_out, rho_m, valid, tile, c0);
                     const int chunk0 = (nbk * p.nb + c0) >> 3;
                     uint32_t r[32];
                     tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
                     tmem_ld_wait();
-                    uint4 o[4];
                     if (valid) {
+                        const uint32_t mbits = masks[item];
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
                             float v[8];
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[g * 8 + e]);
-                            if (p.mode == 0) {
-                                const float4 b0 = bv[2 * g], b1 = bv[2 * g + 1];
-                                v[0] = fmaxf(v[0] + b0.x, 0.f); v[1] = fmaxf(v[1] + b0.y, 0.f);
-                                v[2] = fmaxf(v[2] + b0.z, 0.f); v[3] = fmaxf(v[3] + b0.w, 0.f);
-                                v[4] = fmaxf(v[4] + b1.x, 0.f); v[5] = fmaxf(v[5] + b1.y, 0.f);
-                                v[6] = fmaxf(v[6] + b1.z, 0.f); v[7] = fmaxf(v[7] + b1.w, 0.f);
-                            } else {
-                                const uint32_t mw[4] = {mk[g].x, mk[g].y, mk[g].z, mk[g].w};
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) {
-                                    const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
-                                    // bf16 > 0  <=>  sign bit clear and not zero
-                                    if (!(h != 0 && (h & 0x8000u) == 0)) v[e] = 0.f;
-                                }
+                            for (int e = 0; e < 8; ++e) {
+                                v[e] = __uint_as_float(r[g * 8 + e]);
+                                if (p.mode == 0) v[e] = fmaxf(v[e], 0.f);
+                                else if (!((mbits >> (g * 8 + e)) & 1u)) v[e] = 0.f;
                             }
+                            uint4 o;
                             __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
                             __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
-                            o[g].x = *reinterpret_cast<uint32_t *>(&t0); o[g].y = *reinterpret_cast<uint32_t *>(&t1);
-                            o[g].z = *reinterpret_cast<uint32_t *>(&t2); o[g].w = *reinterpret_cast<uint32_t *>(&t3);
+                            o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
+                            o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
+                            *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk0 + g) * p.R_out + rho_out) * 8) = o;
                         }
-                    }
-                    if (item + 1 < items) load_aux(item + 1);      // next item's aux loads overlap this item's stores
-                    if (valid) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g)
-                            *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk0 + g) * p.R_out + rho_out) * 8) = o[g];
                     }
                 }
                 tc_fence_before();
                 __syncwarp();
                 if (a == 0 && threadIdx.x == 64) DBG_STAMP(6);
-                if (lane == 0) mbar_arrive(&acc_empty);
             }
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, 512);
+    if (threadIdx.x == 0 && p.dbg) p.dbg[148 * 8 + blockIdx.x * 2 + 1] = dg_globaltimer();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -321,6 +348,7 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
     // channel chunks of dZ this M block really has (the rest of the 128 lanes accumulate garbage that is never stored)
     const int a_chunks = min(16, chunks_dz - mblk * 16);
 
+    dg_pdl_launch_dependents();
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); }
         mbar_init(&acc_full, 1);
@@ -331,6 +359,7 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
+    dg_pdl_wait();
 
     if (warp == 0) {
         uint32_t s = 0, ph = 0;
@@ -525,8 +554,10 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     float *ws = reinterpret_cast<float *>(smem + ((img_bytes + 1023) & ~1023u));    // [9][C]
     float *gws = ws + 9 * p.C;                                                         // [9][C] partial weight gradient
 
+    dg_pdl_launch_dependents();
     if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
     __syncthreads();
+    dg_pdl_wait();
     if (tid == 0) {
         mbar_arrive_expect_tx(&bar, img_bytes);
         const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
@@ -671,6 +702,8 @@ __global__ void __launch_bounds__(384) encode_blocked_kernel(const uint8_t *__re
                                                             const uint8_t *__restrict__ rank, const uint8_t *__restrict__ sym,
                                                             bf16 *__restrict__ out, int R, int pitch, int pad) {
     const int n = blockIdx.x, p = threadIdx.x;
+    dg_pdl_launch_dependents();
+    dg_pdl_wait();
     if (p >= DG_POINTS) return;
     const int src = dg_src_point_d(p, sym ? sym[n] : 0);
     const uint8_t *rec = raw + (size_t)n * DG_RAW_PLANES * DG_POINTS;
@@ -736,6 +769,8 @@ struct PackLayer {
 };
 
 __global__ void __launch_bounds__(256) pack_layer_kernel(const PackLayer *__restrict__ table, int R_out, int pitch_out, int pad_out) {
+    dg_pdl_launch_dependents();
+    dg_pdl_wait();
     const PackLayer pl = table[blockIdx.y];
     const float *__restrict__ W = pl.W, *__restrict__ b = pl.b, *__restrict__ a = pl.a;
     bf16 *__restrict__ wf = pl.wf, *__restrict__ wd = pl.wd;
@@ -809,7 +844,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     dg_ctx *c = m->ctx;
     static long long *dbg = nullptr;
     static const bool timeline = getenv("DG_TIMELINE") != nullptr;
-    if (timeline && !dbg) cudaMalloc(&dbg, 148 * 8 * sizeof(long long));
+    if (timeline && !dbg) cudaMalloc(&dbg, 148 * 10 * sizeof(long long));
     cp.dbg = timeline ? dbg : nullptr;
     const size_t img_bytes = ((size_t)(cp.cin / 8) * cp.R_in * 16 + 1023) & ~(size_t)1023;
     const size_t stage = (size_t)cp.kp * cp.nb * 2;
@@ -821,17 +856,25 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     const size_t smem = img_bytes + ns * stage;
     const int grid = cp.n < m->bf->num_sms ? cp.n : m->bf->num_sms;
     { dg_prof_scope _ps(c, cp.mode ? DG_K_DGRAD : (cp.ksize == 5 || cp.cin < cp.cout ? DG_K_CONV_FIRST : DG_K_CONV));
-    conv_umma_kernel<<<grid, 320, smem, c->stream>>>(cp);
+    DG_CUDA(dg_launch_pdl(conv_umma_kernel, dim3(grid), dim3(320), smem, c->stream, cp));
     }
     c->launches++;
     if (timeline) {
-        std::vector<long long> h(148 * 8);
+        std::vector<long long> h(148 * 10);
         cudaStreamSynchronize(c->stream);
         cudaMemcpy(h.data(), dbg, h.size() * 8, cudaMemcpyDeviceToHost);
         double d[7] = {0};
         for (int b = 0; b < grid; ++b) for (int i = 1; i < 7; ++i) d[i] += (double)(h[b * 8 + i] - h[b * 8]) / grid;
         double w = 0;
         for (int b = 0; b < grid; ++b) w += (double)h[b * 8 + 7] / grid;
+        long long t0min = h[148 * 8], t0max = h[148 * 8], t1max = h[148 * 8 + 1], t1min = h[148 * 8 + 1], dmax = 0, dmin = 1ll << 60;
+        for (int b = 0; b < grid; ++b) {
+            const long long a0 = h[148 * 8 + 2 * b], a1 = h[148 * 8 + 2 * b + 1];
+            t0min = std::min(t0min, a0); t0max = std::max(t0max, a0); t1max = std::max(t1max, a1); t1min = std::min(t1min, a1);
+            dmax = std::max(dmax, a1 - a0); dmin = std::min(dmin, a1 - a0);
+        }
+        fprintf(stderr, "   globaltimer ns: CTA start spread %lld, first start -> last end %lld, first end -> last end %lld, CTA duration min %lld max %lld\n",
+                t0max - t0min, t1max - t0min, t1max - t1min, dmin, dmax);
         fprintf(stderr, "conv timeline (cycles since CTA start, mean over %d CTAs) mode=%d k=%d: setup %.0f | img panel0 %.0f panel1 %.0f | mma issued %.0f | acc ready %.0f | epilogue done %.0f | weight-wait %.0f\n",
                 grid, cp.mode, cp.ksize, d[1], d[2], d[3], d[4], d[5], d[6], w);
     }
@@ -939,7 +982,7 @@ int dg_bf16_params_changed(dg_model *m) {
     dg_ctx *c = m->ctx;
     {
         dg_prof_scope _ps(c, DG_K_PACK);
-        pack_layer_kernel<<<dim3(b->num_sms, m->L - 1), 256, 0, c->stream>>>(b->pack_table, DG_R3, b->g3.pitch, b->g3.pad);
+        DG_CUDA(dg_launch_pdl(pack_layer_kernel, dim3(b->num_sms, m->L - 1), dim3(256), 0, c->stream, (const PackLayer *)b->pack_table, (int)DG_R3, b->g3.pitch, b->g3.pad));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
@@ -950,7 +993,7 @@ int dg_bf16_stage_raw(dg_model *m) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
     { dg_prof_scope _ps(c, DG_K_ENCODE);
-    encode_blocked_kernel<<<m->n, 384, 0, c->stream>>>(m->d_raw, m->d_player, m->d_rank, m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad);
+    DG_CUDA(dg_launch_pdl(encode_blocked_kernel, dim3(m->n), dim3(384), 0, c->stream, (const uint8_t *)m->d_raw, (const uint8_t *)m->d_player, (const uint8_t *)m->d_rank, (const uint8_t *)m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
@@ -988,7 +1031,7 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     const size_t smem = (((size_t)(m->C / 8) * DG_R3 * 16 + 1023) & ~(size_t)1023) + (size_t)18 * m->C * 4;
     DG_REQUIRE(smem <= 227 * 1024 - 4096, "bf16 path: head image does not fit shared memory (C=%d)", m->C);
     { dg_prof_scope _ps(c, DG_K_HEAD);
-    head_bf16_kernel<<<m->n, 384, smem, c->stream>>>(hp);
+    DG_CUDA(dg_launch_pdl(head_bf16_kernel, dim3(m->n), dim3(384), smem, c->stream, hp));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
@@ -1025,6 +1068,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + lh.offW, lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS)) return rc;
     }
     int cur = 0;                                           // dZ_{L-1} is in dz[0] (or dz1 when L-1 == 1)
+    bool rec_bias[2] = {false, false}, rec_reduce[2] = {false, false};   // events recorded in THIS pass (stream capture forbids waiting on older records)
     for (int l = m->L - 2; l >= 0; --l) {                  // conv layer index l (0-based) = layer l+1
         const LayerInfo &li = m->layers[l];
         const LayerOps &o = b->ops[l];
@@ -1043,6 +1087,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
             c->launches++;
         }
         DG_CUDA(cudaEventRecord(b->ev_bias[par], b->side));
+        rec_bias[par] = true;
         {
             WgradPlan w;
             if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
@@ -1052,9 +1097,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
             wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
             wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
             // this scratch half was last read by the reduction two layers ago
-            DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
+            if (rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
             { dg_prof_scope _ps(c, DG_K_WGRAD);
-            wgrad_umma_kernel<<<w.combos * w.splits, 192, w.smem, c->stream>>>(wp);
+            DG_CUDA(dg_launch_pdl(wgrad_umma_kernel, dim3(w.combos * w.splits), dim3(192), w.smem, c->stream, wp));
             }
             c->launches++;
             DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
@@ -1065,11 +1110,12 @@ int dg_bf16_backward(dg_model *m, float scale) {
             }
             c->launches++;
             DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
+            rec_reduce[par] = true;
         }
         // the layer's gradient slice is final once the side stream has run both kernels
         if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + li.offW, li.nW + li.cout + (size_t)li.cout * DG_POINTS, b->side)) return rc;
         // the next dgrad overwrites the dZ buffer that the bias-gradient kernel of the layer above was reading
-        DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_bias[par ^ 1], 0));
+        if (rec_bias[par ^ 1]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_bias[par ^ 1], 0));
         if (l >= 1) {
             // dZ_{l} -> dZ_{l-1}: transposed conv with flipped taps, masked by ReLU of layer l's input h_l
             const bool into_first = (l - 1) == 0;

@@ -69,6 +69,7 @@ __global__ void __launch_bounds__(384) encode_bits_kernel(const uint8_t *__restr
 __global__ void labels_kernel(const uint8_t *__restrict__ x, const uint8_t *__restrict__ y, const uint8_t *__restrict__ sym,
                               int n, int32_t *__restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    dg_pdl_wait();
     if (i >= n) return;
     int a = x[i] - 1, b = y[i] - 1;
     const int s = sym ? sym[i] : 0;

@@ -19,6 +19,11 @@ struct dg_model {
     int32_t *d_targets = nullptr, *d_argmax = nullptr;
     float *d_logp = nullptr, *d_loss_n = nullptr, *d_loss = nullptr;
     int *d_errors = nullptr;
+    // captured CUDA graph of one fused training step (bf16 path, single GPU)
+    cudaGraphExec_t step_graph = nullptr;
+    int step_graph_n = 0;
+    long long step_graph_launches = 0;
+    float *d_rate = nullptr, *h_rate = nullptr;     // rate for the graph's SGD node (device scalar, pinned staging)
     // fp32 path (NCHW)
     std::vector<float *> act;          // act[0] = input planes, act[l] = h_l
     float *dz[2] = {nullptr, nullptr};
