@@ -87,6 +87,15 @@ class Context:
         check(self.L.dg_encode(self.h, rp, pp, kp, sp, n, ffi.cast("void *", out.ctypes.data), fmt))
         return out
 
+    def encode_noalloc(self, raw, player, rank, sym=None, fmt=DG_FMT_F32_NCHW):
+        """dg_encode_noalloc: same result as encode() for up to 64 positions, staged through the library's fixed
+        device array instead of an allocated buffer (for callers that must not cudaMalloc)."""
+        ra, rp = _u8(raw); pa, pp = _u8(player); ka, kp = _u8(rank); sa, sp = _opt_u8(sym)
+        n = len(pa)
+        out = np.empty((n, 37, 19, 19), np.float32) if fmt == DG_FMT_F32_NCHW else np.empty((n, 37, 12), np.uint32)
+        check(self.L.dg_encode_noalloc(self.h, rp, pp, kp, sp, n, ffi.cast("void *", out.ctypes.data), fmt))
+        return out
+
     def summarize_boards(self, stones):
         sa, sp = _u8(stones)
         n = sa.reshape(-1, 19, 19).shape[0]
