@@ -35,17 +35,23 @@ static Geom geom_for(int k) {
 // ---------------------------------------------------------------------------------------------
 // conv forward / input gradient
 // ---------------------------------------------------------------------------------------------
+#define CONV_MAX_CHAIN 16
 struct ConvParams {
-    const bf16 *in;       // [n][cin/8][R_in][8]
-    const bf16 *w;        // [taps][cin/8][cout][8]
-    bf16 *out;            // [n][cout/8][R_out][8]
-    const float *bias;    // mode 0: [cout/8][R_out][8] fp32, b[c] + a[c][x][y]
-    const bf16 *mask;     // mode 1: [n][cout/8][R_mask][8], output kept where mask > 0
+    const bf16 *in;                    // [n][cin/8][R_in][8]  input image of the first layer of the chain
+    // A chain is `nchain` consecutive layers run by one kernel with the activation image resident in shared memory:
+    // layer j's epilogue writes its output rows back over the image (all MMAs of layer j are complete by then) and
+    // layer j+1 starts from there -- no launch, no image reload, the weight ring keeps streaming across layers.
+    // nchain > 1 needs cin == cout <= 128 (one N block, one K panel) and the 3x3 geometry in and out.
+    const bf16 *w[CONV_MAX_CHAIN];     // [taps][cin/8][cout][8]
+    bf16 *out[CONV_MAX_CHAIN];         // [n][cout/8][R_out][8]   every layer's output also goes to HBM (backward needs it)
+    const float *bias[CONV_MAX_CHAIN]; // mode 0: [cout/8][R_out][8] fp32, b[c] + a[c][x][y]
+    const bf16 *mask[CONV_MAX_CHAIN];  // mode 1: [n][cout/8][R_mask][8], output kept where mask > 0
+    int nchain;
     int n, cin, cout;
     int R_in, pitch_in, pad_in, ksize, first, ntiles;
-    int R_out, pitch_out, pad_out;
+    int R_out, pitch_out, pad_out;     // geometry of the LAST layer's HBM output (intermediate layers: same as the input)
     int R_mask, pitch_mask, pad_mask;
-    int nb;               // N block (<= 256, multiple of 16); cout % nb == 0
+    int nb;               // N block (<= 128, multiple of 32); cout % nb == 0
     int kp;               // channels per weight ring stage (multiple of 16); cin % kp == 0
     int nstages;
     int mode;
@@ -54,10 +60,11 @@ struct ConvParams {
 
 #define DBG_STAMP(slot) do { if (p.dbg) p.dbg[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
 __device__ __forceinline__ long long dg_globaltimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define CHAIN_STAMP(l, k) do { if (p.dbg && blockIdx.x == 0) p.dbg[148 * 10 + (l) * 4 + (k)] = clock64(); } while (0)
 #define CONV_MAX_STAGES 8
 #define CONV_MAX_KPANELS 4
 
-__global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
+__global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES];
     __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_empty, acc_full, acc_ready;
@@ -112,28 +119,29 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
                 }
             }
             __syncwarp();
-            for (int nbk = 0; nbk < nnb; ++nbk) {
-                const uint8_t *w_k = (const uint8_t *)p.w + (size_t)nbk * p.nb * 16;
-                for (int k = 0; k < nkp; ++k, w_k += kp_stride) {
-                    const uint8_t *wsrc = w_k;
-                    for (int t = 0; t < taps; ++t, wsrc += tap_stride) {
-                        mbar_wait(&w_empty[s], ph ^ 1);
-                        if (elect_one()) {
-                            mbar_arrive_expect_tx(&w_full[s], stage_bytes);
-                            uint8_t *dst = ring + (size_t)s * stage_bytes;
-                            // W[t][k*chunks_kp + c][nbk*nb .. +nb][8]
-                            if (nnb == 1) {
-                                bulk_g2s(dst, wsrc, stage_bytes, &w_full[s]);
-                            } else {
-                                for (int c = 0; c < chunks_kp; ++c)
-                                    bulk_g2s(dst + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
+            for (int l = 0; l < p.nchain; ++l)
+                for (int nbk = 0; nbk < nnb; ++nbk) {
+                    const uint8_t *w_k = (const uint8_t *)p.w[l] + (size_t)nbk * p.nb * 16;
+                    for (int k = 0; k < nkp; ++k, w_k += kp_stride) {
+                        const uint8_t *wsrc = w_k;
+                        for (int t = 0; t < taps; ++t, wsrc += tap_stride) {
+                            mbar_wait(&w_empty[s], ph ^ 1);
+                            if (elect_one()) {
+                                mbar_arrive_expect_tx(&w_full[s], stage_bytes);
+                                uint8_t *dst = ring + (size_t)s * stage_bytes;
+                                // W[t][k*chunks_kp + c][nbk*nb .. +nb][8]
+                                if (nnb == 1) {
+                                    bulk_g2s(dst, wsrc, stage_bytes, &w_full[s]);
+                                } else {
+                                    for (int c = 0; c < chunks_kp; ++c)
+                                        bulk_g2s(dst + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
+                                }
                             }
+                            __syncwarp();
+                            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
                         }
-                        __syncwarp();
-                        if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
                     }
                 }
-            }
         }
     } else if (warp == 1) {
         // ===== MMA warp (converged, so descriptors stay in uniform registers; one elected lane issues) =====
@@ -149,159 +157,241 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
         uint32_t b_lo_s = b_lo_ring;
         long long wait_cycles = 0;
         for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
-            for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                // the epilogue warps have drained the previous accumulators and, in forward mode, pre-loaded the new ones
-                // with the bias, so every forward MMA accumulates
-                mbar_wait(&acc_ready, a & 1);
-                tc_fence_after();
-                uint32_t a_lo_k = a_lo_first;
-                uint32_t first_mma = p.mode == 0 ? 1u : 0u;       // 0 until the first MMA of this accumulator set has been issued
-                for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
-                    if (nbk == 0) { mbar_wait(&img_full[k], j & 1); if (j == 0 && lane == 0) DBG_STAMP(2 + (k > 0)); }
-                    uint32_t a_lo_ky = a_lo_k;                    // + ky*pitch + kx rows, in 16-byte units
-                    for (int ky = 0; ky < p.ksize; ++ky, a_lo_ky += p.pitch_in) {
-                        for (int kx = 0; kx < p.ksize; ++kx) {
-                            const long long tw0 = p.dbg ? clock64() : 0;
-                            mbar_wait(&w_full[s], ph);
-                            if (p.dbg) wait_cycles += clock64() - tw0;
-                            tc_fence_after();
-                            if (elect_one()) {
-                                uint32_t a_tile = a_lo_ky + kx;
-                                uint32_t d_tmem = tmem_base;
-                                for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
-                                    uint32_t a_lo = a_tile, b_lo = b_lo_s;
-#pragma unroll 4
-                                    for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep)
-                                        mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma | (uint32_t)ks);
+            for (int l = 0; l < p.nchain; ++l)
+                for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
+                    // the epilogue warps have drained the previous accumulators, written the previous layer's output rows
+                    // into the shared-memory image (chains) and, in forward mode, pre-loaded the accumulators with the bias
+                    mbar_wait(&acc_ready, a & 1);
+                    tc_fence_after();
+                    if (lane == 0 && j == 0) CHAIN_STAMP(l, 0);
+                    uint32_t a_lo_k = a_lo_first;
+                    uint32_t first_mma = p.mode == 0 ? 1u : 0u;       // 0 until the first MMA of this accumulator set has been issued
+                    // The barrier of stage i+1 is waited for between the two halves of stage i's MMAs, so its latency (and the
+                    // commit / elect bookkeeping) is covered by MMAs already queued on the tensor pipe instead of draining it.
+                    const int kh = ksteps >> 1;                       // first half: k-steps [0, kh), second: [kh, ksteps)
+                    bool stage_ready = false;
+                    for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
+                        if (l == 0 && nbk == 0) { mbar_wait(&img_full[k], j & 1); if (j == 0 && lane == 0) DBG_STAMP(2 + (k > 0)); }
+                        uint32_t a_lo_ky = a_lo_k;                    // + ky*pitch + kx rows, in 16-byte units
+                        for (int ky = 0; ky < p.ksize; ++ky, a_lo_ky += p.pitch_in) {
+                            for (int kx = 0; kx < p.ksize; ++kx) {
+                                if (!stage_ready) {
+                                    const long long tw0 = p.dbg ? clock64() : 0;
+                                    mbar_wait(&w_full[s], ph);
+                                    if (p.dbg) wait_cycles += clock64() - tw0;
+                                    tc_fence_after();
                                 }
-                                mma_commit(&w_empty[s]);
+                                const bool last_stage = (k == nkp - 1) && (ky == p.ksize - 1) && (kx == p.ksize - 1);
+                                const uint32_t s_next = (s + 1 == (uint32_t)p.nstages) ? 0u : s + 1;
+                                const uint32_t ph_next = (s + 1 == (uint32_t)p.nstages) ? ph ^ 1u : ph;
+                                if (elect_one()) {
+                                    uint32_t a_tile = a_lo_ky + kx;
+                                    uint32_t d_tmem = tmem_base;
+                                    for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
+                                        uint32_t a_lo = a_tile, b_lo = b_lo_s;
+#pragma unroll 4
+                                        for (int ks = 0; ks < kh; ++ks, a_lo += a_kstep, b_lo += b_kstep)
+                                            mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma | (uint32_t)ks);
+                                    }
+                                }
+                                __syncwarp();
+                                if (!last_stage) {                    // next stage's weights: wait while this stage's MMAs execute
+                                    mbar_wait(&w_full[s_next], ph_next);
+                                    tc_fence_after();
+                                    stage_ready = true;
+                                } else {
+                                    stage_ready = false;
+                                }
+                                if (elect_one()) {
+                                    uint32_t a_tile = a_lo_ky + kx + (uint32_t)kh * a_kstep;
+                                    uint32_t d_tmem = tmem_base;
+                                    for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
+                                        uint32_t a_lo = a_tile, b_lo = b_lo_s + (uint32_t)kh * b_kstep;
+#pragma unroll 4
+                                        for (int ks = kh; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep)
+                                            mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, 1u);
+                                    }
+                                    mma_commit(&w_empty[s]);
+                                }
+                                __syncwarp();
+                                first_mma = 1;
+                                b_lo_s += stage_units;
+                                s = s_next; ph = ph_next;
+                                if (s == 0) b_lo_s = b_lo_ring;
                             }
-                            __syncwarp();
-                            first_mma = 1;
-                            b_lo_s += stage_units;
-                            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; b_lo_s = b_lo_ring; }
                         }
                     }
+                    if (elect_one()) mma_commit(&acc_full);
+                    __syncwarp();
+                    if (lane == 0 && j == 0) CHAIN_STAMP(l, 1);
+                    if (a == 0 && lane == 0) { DBG_STAMP(4); if (p.dbg) p.dbg[blockIdx.x * 8 + 7] = wait_cycles; }
                 }
-                if (elect_one()) mma_commit(&acc_full);
-                __syncwarp();
-                if (a == 0 && lane == 0) { DBG_STAMP(4); if (p.dbg) p.dbg[blockIdx.x * 8 + 7] = wait_cycles; }
-            }
             if (elect_one()) mma_commit(&img_empty);
             __syncwarp();
         }
     } else {
-        // ===== epilogue warps 2..9: TMEM -> registers -> bias/ReLU or mask -> bf16 -> HBM =====
+        // ===== epilogue warps 2..9: TMEM -> registers -> ReLU or mask -> bf16 -> HBM (+ shared-memory image in a chain) =====
         // warp w may only touch TMEM lanes 32*(w%4)..+31; two warps share a lane quarter and split the 32-column blocks.
         const int q = warp & 3, half = (warp - 2) >> 2;
         const int chunks_out = p.cout >> 3;
         const int nblk32 = p.nb >> 5;
         const int my_blocks = (nblk32 - half + 1) >> 1;           // blocks half, half+2, ...
         const int items = p.ntiles * my_blocks;
+        auto row_of = [&](int item, int l, int &rho, int &rho_out, int &rho_m, bool &valid, int &tile, int &c0) {
+            tile = item / my_blocks;
+            c0 = ((item - tile * my_blocks) * 2 + half) * 32;
+            rho = p.first + tile * 128 + q * 32 + lane;
+            const int xp = rho / p.pitch_in, yp = rho - xp * p.pitch_in;
+            const int x = xp - p.pad_in, y = yp - p.pad_in;
+            valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+            // intermediate layers of a chain keep the input geometry; only the last layer's HBM output may differ
+            rho_out = l == p.nchain - 1 ? (x + p.pad_out) * p.pitch_out + y + p.pad_out : rho;
+            rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
+        };
+        // forward: accumulators start as bias[c] + a[c][x][y] (tcgen05.st), so the drain below has no global load
+        auto preload_bias = [&](int l, int nbk) {
+            for (int item = 0; item < items; ++item) {
+                int rho, rho_out, rho_m, tile, c0; bool valid;
+                row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
+                const int R_b = l == p.nchain - 1 ? p.R_out : p.R_in;
+                const int chunk0 = (nbk * p.nb + c0) >> 3;
+                uint32_t r[32];
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+                    if (valid) {
+                        const float4 *bp = reinterpret_cast<const float4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8);
+                        b0 = __ldg(bp); b1 = __ldg(bp + 1);
+                    }
+                    r[g * 8 + 0] = __float_as_uint(b0.x); r[g * 8 + 1] = __float_as_uint(b0.y);
+                    r[g * 8 + 2] = __float_as_uint(b0.z); r[g * 8 + 3] = __float_as_uint(b0.w);
+                    r[g * 8 + 4] = __float_as_uint(b1.x); r[g * 8 + 5] = __float_as_uint(b1.y);
+                    r[g * 8 + 6] = __float_as_uint(b1.z); r[g * 8 + 7] = __float_as_uint(b1.w);
+                }
+                tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+            }
+            tmem_st_wait();
+        };
+        // one item's bias (32 channels of one row) of layer l into registers
+        auto load_bias_item = [&](int item, int l, float4 (&bq)[8]) {
+            int rho, rho_out, rho_m, tile, c0; bool valid;
+            row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
+            const int R_b = l == p.nchain - 1 ? p.R_out : p.R_in;
+            const int chunk0 = c0 >> 3;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                bq[2 * g] = make_float4(0.f, 0.f, 0.f, 0.f); bq[2 * g + 1] = bq[2 * g];
+                if (valid) {
+                    const float4 *bp = reinterpret_cast<const float4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8);
+                    bq[2 * g] = __ldg(bp); bq[2 * g + 1] = __ldg(bp + 1);
+                }
+            }
+        };
         uint32_t a = 0;
         for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x) {
-            for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                auto row_of = [&](int item, int &rho_out, int &rho_m, bool &valid, int &tile, int &c0) {
-                    tile = item / my_blocks;
-                    c0 = ((item - tile * my_blocks) * 2 + half) * 32;
-                    const int rho = p.first + tile * 128 + q * 32 + lane;
-                    const int xp = rho / p.pitch_in, yp = rho - xp * p.pitch_in;
-                    const int x = xp - p.pad_in, y = yp - p.pad_in;
-                    valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
-                    rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
-                    rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
-                };
-                // ---- before the MMAs: no global load is left for the drain below.
-                // forward: the accumulators start as bias[c] + a[c][x][y] (written to TMEM while the image is still landing);
-                // backward: the ReLU mask of each item is compressed to one 32-bit word while the MMAs run.
-                uint32_t masks[8];
-                if (p.mode == 0) {
-                    for (int item = 0; item < items; ++item) {
-                        int rho_out, rho_m, tile, c0; bool valid;
-                        row_of(item, rho_out, rho_m, valid, tile, c0);
-                        const int chunk0 = (nbk * p.nb + c0) >> 3;
-                        uint32_t r[32];
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-                            if (valid) {
-                                const float4 *bp = reinterpret_cast<const float4 *>(p.bias + ((size_t)(chunk0 + g) * p.R_out + rho_out) * 8);
-                                b0 = __ldg(bp); b1 = __ldg(bp + 1);
-                            }
-                            r[g * 8 + 0] = __float_as_uint(b0.x); r[g * 8 + 1] = __float_as_uint(b0.y);
-                            r[g * 8 + 2] = __float_as_uint(b0.z); r[g * 8 + 3] = __float_as_uint(b0.w);
-                            r[g * 8 + 4] = __float_as_uint(b1.x); r[g * 8 + 5] = __float_as_uint(b1.y);
-                            r[g * 8 + 6] = __float_as_uint(b1.z); r[g * 8 + 7] = __float_as_uint(b1.w);
-                        }
-                        tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+            for (int l = 0; l < p.nchain; ++l)
+                for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
+                    const bool chain_more = l + 1 < p.nchain;      // this layer's output is the next layer's shared-memory image
+                    if (l == 0 || nnb > 1) {
+                        // first layer of a position (or a multi-N-block layer): hand the accumulators to the MMA warp here;
+                        // inside a chain the hand-over happens at the end of the previous layer's drain
+                        if (p.mode == 0) preload_bias(l, nbk);
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc_ready);
                     }
-                    tmem_st_wait();
-                }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&acc_ready);
-                if (p.mode != 0) {
+                    // backward: the ReLU mask of each item is compressed to one 32-bit word while the MMAs run
+                    uint32_t masks[8];
+                    if (p.mode != 0) {
+#pragma unroll
+                        for (int item = 0; item < 8; ++item) {
+                            masks[item] = 0;
+                            if (item < items) {
+                                int rho, rho_out, rho_m, tile, c0; bool valid;
+                                row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
+                                if (valid) {
+                                    const int chunk0 = (nbk * p.nb + c0) >> 3;
+                                    uint32_t mbits = 0;
+#pragma unroll
+                                    for (int g = 0; g < 4; ++g) {
+                                        const uint4 mk = __ldg(reinterpret_cast<const uint4 *>(p.mask[l] + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
+                                        const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+                                        for (int e = 0; e < 8; ++e) {
+                                            const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                                            // bf16 > 0  <=>  sign bit clear and not zero
+                                            if (h != 0 && (h & 0x8000u) == 0) mbits |= 1u << (g * 8 + e);
+                                        }
+                                    }
+                                    masks[item] = mbits;
+                                }
+                            }
+                        }
+                    }
+                    // inside a forward chain the next layer's bias is fetched one item ahead of the drain (the first item while
+                    // the MMAs still run) and written into each accumulator block right after that block has been drained
+                    const bool bias_pipe = chain_more && p.mode == 0;
+                    float4 bq[2][8];
+                    if (bias_pipe) load_bias_item(0, l + 1, bq[0]);
+                    mbar_wait(&acc_full, a & 1);
+                    tc_fence_after();
+                    if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
+                    if (threadIdx.x == 64 && pos == (int)blockIdx.x) CHAIN_STAMP(l, 2);
+                    const int R_o = chain_more ? p.R_in : p.R_out;
 #pragma unroll
                     for (int item = 0; item < 8; ++item) {
-                        masks[item] = 0;
-                        if (item < items) {
-                            int rho_out, rho_m, tile, c0; bool valid;
-                            row_of(item, rho_out, rho_m, valid, tile, c0);
-                            if (valid) {
-                                const int chunk0 = (nbk * p.nb + c0) >> 3;
-                                uint32_t mbits = 0;
+                        if (item >= items) break;
+                        int rho, rho_out, rho_m, tile, c0; bool valid;
+                        row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
+                        const int chunk0 = (nbk * p.nb + c0) >> 3;
+                        uint32_t r[32];
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+                        if (bias_pipe && item + 1 < items) load_bias_item(item + 1, l + 1, bq[(item + 1) & 1]);
+                        tmem_ld_wait();
+                        if (valid) {
+                            const uint32_t mbits = masks[item];
 #pragma unroll
-                                for (int g = 0; g < 4; ++g) {
-                                    const uint4 mk = __ldg(reinterpret_cast<const uint4 *>(p.mask + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
-                                    const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+                            for (int g = 0; g < 4; ++g) {
+                                float v[8];
 #pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
-                                        // bf16 > 0  <=>  sign bit clear and not zero
-                                        if (h != 0 && (h & 0x8000u) == 0) mbits |= 1u << (g * 8 + e);
-                                    }
+                                for (int e = 0; e < 8; ++e) {
+                                    v[e] = __uint_as_float(r[g * 8 + e]);
+                                    if (p.mode == 0) v[e] = fmaxf(v[e], 0.f);
+                                    else if (!((mbits >> (g * 8 + e)) & 1u)) v[e] = 0.f;
                                 }
-                                masks[item] = mbits;
+                                uint4 o;
+                                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+                                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
+                                o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
+                                o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
+                                *reinterpret_cast<uint4 *>(p.out[l] + (((size_t)pos * chunks_out + chunk0 + g) * R_o + rho_out) * 8) = o;
+                                if (chain_more) *reinterpret_cast<uint4 *>(img + ((size_t)(chunk0 + g) * p.R_in + rho) * 16) = o;
                             }
                         }
-                    }
-                }
-                mbar_wait(&acc_full, a & 1);
-                tc_fence_after();
-                if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
+                        if (bias_pipe) {
+                            const float4 (&bb)[8] = bq[item & 1];
 #pragma unroll
-                for (int item = 0; item < 8; ++item) {
-                    if (item >= items) break;
-                    int rho_out, rho_m, tile, c0; bool valid;
-                    row_of(item, rho_out, rho_m, valid, tile, c0);
-                    const int chunk0 = (nbk * p.nb + c0) >> 3;
-                    uint32_t r[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
-                    tmem_ld_wait();
-                    if (valid) {
-                        const uint32_t mbits = masks[item];
-#pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            float v[8];
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                v[e] = __uint_as_float(r[g * 8 + e]);
-                                if (p.mode == 0) v[e] = fmaxf(v[e], 0.f);
-                                else if (!((mbits >> (g * 8 + e)) & 1u)) v[e] = 0.f;
+                            for (int g = 0; g < 8; ++g) {
+                                r[g * 4 + 0] = __float_as_uint(bb[g].x); r[g * 4 + 1] = __float_as_uint(bb[g].y);
+                                r[g * 4 + 2] = __float_as_uint(bb[g].z); r[g * 4 + 3] = __float_as_uint(bb[g].w);
                             }
-                            uint4 o;
-                            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-                            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
-                            o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
-                            o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
-                            *reinterpret_cast<uint4 *>(p.out + (((size_t)pos * chunks_out + chunk0 + g) * p.R_out + rho_out) * 8) = o;
+                            tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
                         }
                     }
+                    if (chain_more) {
+                        // next layer: its accumulators (bias) and its input image are ready once every epilogue warp gets here
+                        if (bias_pipe) tmem_st_wait();
+                        fence_proxy_async();                       // generic-proxy st.shared -> visible to the tensor core's async proxy
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc_ready);
+                    } else {
+                        tc_fence_before();
+                        __syncwarp();
+                    }
+                    if (a == 0 && threadIdx.x == 64) DBG_STAMP(6);
+                    if (threadIdx.x == 64 && pos == (int)blockIdx.x) CHAIN_STAMP(l, 3);
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (a == 0 && threadIdx.x == 64) DBG_STAMP(6);
-            }
         }
     }
     tc_fence_before();
@@ -314,23 +404,29 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const ConvParams p) {
 // weight gradient: D[co][ci] per tap, split-K over (position, 64-row panel) units, partial tiles to
 // scratch, then a deterministic reduction into the Torch7-order gradient vector.
 // ---------------------------------------------------------------------------------------------
+#define WG_MAX_LAYERS 16
 struct WgradParams {
-    const bf16 *dz;       // [n][cout/8][R][8]   (A, MN-major: M = cout channel)
-    const bf16 *x;        // [n][cin/8][R][8]    (B, MN-major: N = cin channel)
-    float *scratch;       // [combo][split][k taps][128][nb]
+    // A launch covers `nl` layers of identical shape: every CTA keeps its (kernel row ky, split) role and walks the layers,
+    // so launch, prologue and the tail of the L2 reductions are paid once and the panel ring never drains between layers.
+    const bf16 *dz[WG_MAX_LAYERS];   // [n][cout/8][R][8]   (A, MN-major: M = cout channel)
+    const bf16 *x[WG_MAX_LAYERS];    // [n][cin/8][R][8]    (B, MN-major: N = cin channel)
+    float *gacc[WG_MAX_LAYERS];      // default path: fp32 accumulation buffer of the layer [tap][cin/4][cout][4], updated with 16-byte reductions
+    float *scratch;       // deterministic path (nl == 1, gacc[0] == NULL): partial tiles [combo][split][kx][nb/4][128][4]
+    int nl;
     int n, cin, cout;     // cin padded (multiple of 16)
     int R, pitch, pad, ksize, first, ntiles;
     int nb;               // N block (cin % nb == 0), k*nb <= 512
     int n_mblk, n_nblk;   // cout / 128 (rounded up), cin / nb
     int splits;           // split-K CTAs per combo
     int nstages;
+    long long *dbg;       // optional timeline (DG_TIMELINE=1): per CTA {start, mma-loop start, mma-loop end, total wait, end}
 };
 
 #define WG_RP 128         // K rows per stage
 
-__global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p) {
+__global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full;
+    __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full, acc_empty;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -339,7 +435,7 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
     const int nblk = combo % p.n_nblk, mblk = (combo / p.n_nblk) % p.n_mblk, ky = combo / (p.n_nblk * p.n_mblk);
     const int rb = WG_RP + 2 * p.pad;                         // B panel rows incl. the kx halo
     const int rb_pad = (rb + 7) & ~7;
-    const uint32_t a_bytes = 16u * WG_RP * 16;                // 16 channel chunks (M = 128) x 64 rows
+    const uint32_t a_bytes = 16u * WG_RP * 16;                // 16 channel chunks (M = 128) x WG_RP rows
     const uint32_t b_bytes = (uint32_t)(p.nb >> 3) * rb_pad * 16;
     const uint32_t stage_bytes = a_bytes + b_bytes;
     const int panels = p.ntiles * 128 / WG_RP;
@@ -349,9 +445,11 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
     const int a_chunks = min(16, chunks_dz - mblk * 16);
 
     dg_pdl_launch_dependents();
+    if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8] = clock64();
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); }
         mbar_init(&acc_full, 1);
+        mbar_init(&acc_empty, 8);
         fence_barrier_init();
     }
     if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
@@ -363,100 +461,201 @@ __global__ void __launch_bounds__(192, 1) wgrad_umma_kernel(const WgradParams p)
 
     if (warp == 0) {
         uint32_t s = 0, ph = 0;
-        int pos = split / panels, panel = split - pos * panels;          // one division up front, counters afterwards
+        const int pos0 = split / panels, panel0 = split - pos0 * panels;   // one division up front, counters afterwards
         const int dpos = p.splits / panels, dpanel = p.splits - dpos * panels;
         const int brow_off = (ky - p.pad) * p.pitch - p.pad;
         const uint32_t tx = (uint32_t)a_chunks * WG_RP * 16 + (uint32_t)(p.nb >> 3) * rb * 16;
-        for (int u = split; u < units; u += p.splits) {
-            mbar_wait(&s_empty[s], ph ^ 1);
-            if (elect_one()) {
-                mbar_arrive_expect_tx(&s_full[s], tx);
-                uint8_t *sa = smem + (size_t)s * stage_bytes, *sb = sa + a_bytes;
-                const int row0 = p.first + panel * WG_RP;
-                const uint8_t *asrc = (const uint8_t *)p.dz + (((size_t)pos * chunks_dz + mblk * 16) * p.R + row0) * 16;
-                for (int c = 0; c < a_chunks; ++c, asrc += (size_t)p.R * 16)
-                    bulk_g2s(sa + (size_t)c * WG_RP * 16, asrc, WG_RP * 16, &s_full[s]);
-                const uint8_t *bsrc = (const uint8_t *)p.x + (((size_t)pos * chunks_x + nblk * (p.nb >> 3)) * p.R + row0 + brow_off) * 16;
-                for (int c = 0; c < (p.nb >> 3); ++c, bsrc += (size_t)p.R * 16)
-                    bulk_g2s(sb + (size_t)c * rb_pad * 16, bsrc, (uint32_t)rb * 16, &s_full[s]);
+        for (int li = 0; li < p.nl; ++li) {
+            int pos = pos0, panel = panel0;
+            for (int u = split; u < units; u += p.splits) {
+                mbar_wait(&s_empty[s], ph ^ 1);
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(&s_full[s], tx);
+                    uint8_t *sa = smem + (size_t)s * stage_bytes, *sb = sa + a_bytes;
+                    const int row0 = p.first + panel * WG_RP;
+                    const uint8_t *asrc = (const uint8_t *)p.dz[li] + (((size_t)pos * chunks_dz + mblk * 16) * p.R + row0) * 16;
+                    for (int c = 0; c < a_chunks; ++c, asrc += (size_t)p.R * 16)
+                        bulk_g2s(sa + (size_t)c * WG_RP * 16, asrc, WG_RP * 16, &s_full[s]);
+                    const uint8_t *bsrc = (const uint8_t *)p.x[li] + (((size_t)pos * chunks_x + nblk * (p.nb >> 3)) * p.R + row0 + brow_off) * 16;
+                    for (int c = 0; c < (p.nb >> 3); ++c, bsrc += (size_t)p.R * 16)
+                        bulk_g2s(sb + (size_t)c * rb_pad * 16, bsrc, (uint32_t)rb * 16, &s_full[s]);
+                }
+                __syncwarp();
+                if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
+                pos += dpos; panel += dpanel;
+                if (panel >= panels) { panel -= panels; ++pos; }
             }
-            __syncwarp();
-            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
-            pos += dpos; panel += dpanel;
-            if (panel >= panels) { panel -= panels; ++pos; }
         }
     } else if (warp == 1) {
         const uint32_t idesc = make_idesc_bf16(128, p.nb, 1, 1);
         const uint32_t hi_a = desc_hi(WG_RP * 16), hi_b = desc_hi((uint32_t)rb_pad * 16);
         const uint32_t a_lo_ring = desc_lo(smem_u32(smem), 128), b_lo_ring = desc_lo(smem_u32(smem) + a_bytes, 128);
         const uint32_t stage_units = stage_bytes >> 4;
-        uint32_t s = 0, ph = 0, acc = 0;
+        uint32_t s = 0, ph = 0;
         uint32_t a_lo_s = a_lo_ring, b_lo_s = b_lo_ring;
-        for (int u = split; u < units; u += p.splits) {
-            mbar_wait(&s_full[s], ph);
+        long long wcy = 0;
+        if (lane == 0 && p.dbg) p.dbg[blockIdx.x * 8 + 1] = clock64();
+        for (int li = 0; li < p.nl; ++li) {
+            mbar_wait(&acc_empty, (li & 1) ^ 1);              // the drain warps have read the previous layer's accumulators
             tc_fence_after();
-            if (elect_one()) {
-                uint32_t d_tmem = tmem_base;
-                for (int kx = 0; kx < p.ksize; ++kx, d_tmem += p.nb) {
-                    uint32_t a_lo = a_lo_s, b_lo = b_lo_s + kx;
+            uint32_t acc = 0;
+            for (int u = split; u < units; u += p.splits) {
+                const long long tw0 = p.dbg ? clock64() : 0;
+                mbar_wait(&s_full[s], ph);
+                if (p.dbg) wcy += clock64() - tw0;
+                tc_fence_after();
+                if (elect_one()) {
+                    uint32_t d_tmem = tmem_base;
+                    for (int kx = 0; kx < p.ksize; ++kx, d_tmem += p.nb) {
+                        uint32_t a_lo = a_lo_s, b_lo = b_lo_s + kx;
 #pragma unroll
-                    for (int ks = 0; ks < WG_RP / 16; ++ks, a_lo += 16, b_lo += 16)
-                        mma_bf16(d_tmem, desc_join(a_lo, hi_a), desc_join(b_lo, hi_b), idesc, acc | (uint32_t)ks);
+                        for (int ks = 0; ks < WG_RP / 16; ++ks, a_lo += 16, b_lo += 16)
+                            mma_bf16(d_tmem, desc_join(a_lo, hi_a), desc_join(b_lo, hi_b), idesc, acc | (uint32_t)ks);
+                    }
+                    mma_commit(&s_empty[s]);
                 }
-                mma_commit(&s_empty[s]);
+                __syncwarp();
+                acc = 1;
+                a_lo_s += stage_units; b_lo_s += stage_units;
+                if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; a_lo_s = a_lo_ring; b_lo_s = b_lo_ring; }
             }
+            if (elect_one()) mma_commit(&acc_full);
             __syncwarp();
-            acc = 1;
-            a_lo_s += stage_units; b_lo_s += stage_units;
-            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; a_lo_s = a_lo_ring; b_lo_s = b_lo_ring; }
         }
-        if (elect_one()) mma_commit(&acc_full);
-        __syncwarp();
+        if (lane == 0 && p.dbg) { p.dbg[blockIdx.x * 8 + 2] = clock64(); p.dbg[blockIdx.x * 8 + 3] = wcy; }
     } else {
-        const int q = warp & 3;
-        mbar_wait(&acc_full, 0);
-        tc_fence_after();
+        // ===== drain warps 2..9: two warps per TMEM lane quarter, alternating 32-column blocks =====
+        const int q = warp & 3, half = (warp - 2) >> 2;
         const bool any = split < units;                       // a CTA without units holds an unwritten accumulator
-        float *dst = p.scratch + (((size_t)combo * p.splits + split) * p.ksize * 128 + (q * 32 + lane)) * p.nb;
-        for (int kx = 0; kx < p.ksize; ++kx)
-            for (int c0 = 0; c0 < p.nb; c0 += 32) {
-                uint32_t r[32];
-                const int ncol = min(32, p.nb - c0);              // nb is a multiple of 16
-                const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + kx * p.nb + c0;
-                if (ncol == 32) tmem_ld32(ta, r); else tmem_ld16(ta, r);
-                tmem_ld_wait();
-                float4 *o = reinterpret_cast<float4 *>(dst + (size_t)kx * 128 * p.nb + c0);
+        const int co = mblk * 128 + q * 32 + lane;
+        const int cin4 = p.cin >> 2;
+        for (int li = 0; li < p.nl; ++li) {
+            mbar_wait(&acc_full, li & 1);
+            tc_fence_after();
+            float4 *gl = reinterpret_cast<float4 *>(p.gacc[li]);
+            // scratch tile layout [kx][ci/4][co][4]: lane = co, so one warp-wide 16-byte access covers 512 contiguous bytes
+            float4 *sc = reinterpret_cast<float4 *>(p.scratch) + ((size_t)combo * p.splits + split) * p.ksize * 32 * p.nb + (q * 32 + lane);
+            for (int kx = 0; kx < p.ksize; ++kx)
+                for (int c0 = half * 32; c0 < p.nb; c0 += 64) {
+                    uint32_t r[32];
+                    const int ncol = min(32, p.nb - c0);          // nb is a multiple of 16
+                    const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + kx * p.nb + c0;
+                    if (ncol == 32) tmem_ld32(ta, r); else tmem_ld16(ta, r);
+                    tmem_ld_wait();
+                    if (gl) {
+                        // default: add this CTA's partial tile straight into the layer's accumulation buffer with vector reductions
+                        // (red.global.add.v4.f32, resolved in L2): no partial-tile round trip through memory, no reduction kernel
+                        if (any && co < p.cout) {
+                            float4 *o = gl + ((size_t)(ky * p.ksize + kx) * cin4 + nblk * (p.nb >> 2) + (c0 >> 2)) * p.cout + co;
 #pragma unroll
-                for (int g = 0; g < 8; ++g)
-                    if (g * 4 < ncol)
-                        o[g] = any ? make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]), __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]))
-                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
+                            for (int g = 0; g < 8; ++g)
+                                if (g * 4 < ncol)
+                                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + (size_t)g * p.cout), "f"(__uint_as_float(r[g * 4])),
+                                                 "f"(__uint_as_float(r[g * 4 + 1])), "f"(__uint_as_float(r[g * 4 + 2])), "f"(__uint_as_float(r[g * 4 + 3]))
+                                                 : "memory");
+                        }
+                    } else {
+                        float4 *o = sc + ((size_t)kx * (p.nb >> 2) + (c0 >> 2)) * 128;
+#pragma unroll
+                        for (int g = 0; g < 8; ++g)
+                            if (g * 4 < ncol)
+                                o[(size_t)g * 128] = any ? make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]), __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]))
+                                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty);
+        }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, 512);
+    if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8 + 4] = clock64();
 }
 
 // gW[(co*cin_true + ci)*KK + ky*k + kx] += sum_split scratch[combo(ky,mblk,nblk)][split][kx][co%128][ci%nb]
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float *__restrict__ scratch, float *__restrict__ gW, int cin_true, int cin,
                                                            int cout, int ksize, int nb, int n_mblk, int n_nblk, int splits) {
-    const int total = ksize * ksize * cout * cin;
-    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
-        const int ci = idx % cin, co = (idx / cin) % cout, t = idx / (cin * cout);
-        if (ci >= cin_true) continue;
+    // scratch tile layout per (combo, split): [kx][ci/4][co%128][4].  A block sums one (tap, 64 co, 16 ci) tile over the
+    // splits with co-fastest threads (coalesced 16-byte reads), transposes it in shared memory and adds it to the Torch7-order
+    // gradient with ci-fastest threads (neighbouring threads 36 bytes apart instead of a whole weight row).
+    __shared__ float tile[64][17];
+    const int KK = ksize * ksize;
+    const int co_tiles = (cout + 63) >> 6, ci_tiles = cin >> 4;
+    const int ntiles = KK * co_tiles * ci_tiles;
+    const size_t st4 = (size_t)ksize * 32 * nb;                      // float4s between consecutive splits
+    const float4 *sc4 = reinterpret_cast<const float4 *>(scratch);
+    for (int tl = blockIdx.x; tl < ntiles; tl += gridDim.x) {
+        const int cit = tl % ci_tiles, cot = (tl / ci_tiles) % co_tiles, t = tl / (ci_tiles * co_tiles);
         const int ky = t / ksize, kx = t - ky * ksize;
-        const int combo = (ky * n_mblk + co / 128) * n_nblk + ci / nb;
-        const float *src = scratch + (((size_t)combo * splits * ksize + kx) * 128 + (co & 127)) * nb + (ci % nb);
-        const size_t st = (size_t)ksize * 128 * nb;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        int sp = 0;
-        for (; sp + 4 <= splits; sp += 4) {
-            s0 += src[(size_t)sp * st]; s1 += src[(size_t)(sp + 1) * st];
-            s2 += src[(size_t)(sp + 2) * st]; s3 += src[(size_t)(sp + 3) * st];
+        {
+            const int co = cot * 64 + (threadIdx.x & 63), c4l = threadIdx.x >> 6, ci = cit * 16 + c4l * 4;
+            float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+            if (co < cout) {
+                const int combo = (ky * n_mblk + co / 128) * n_nblk + ci / nb;
+                const float4 *src = sc4 + (size_t)combo * splits * st4 + ((size_t)kx * (nb >> 2) + ((ci % nb) >> 2)) * 128 + (co & 127);
+                int sp = 0;
+#pragma unroll 4
+                for (; sp + 2 <= splits; sp += 2) {
+                    const float4 a = __ldg(src + (size_t)sp * st4), b = __ldg(src + (size_t)(sp + 1) * st4);
+                    s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
+                    s1.x += b.x; s1.y += b.y; s1.z += b.z; s1.w += b.w;
+                }
+                if (sp < splits) {
+                    const float4 a = __ldg(src + (size_t)sp * st4);
+                    s0.x += a.x; s0.y += a.y; s0.z += a.z; s0.w += a.w;
+                }
+            }
+            float *tr = &tile[threadIdx.x & 63][c4l * 4];
+            tr[0] = s0.x + s1.x; tr[1] = s0.y + s1.y; tr[2] = s0.z + s1.z; tr[3] = s0.w + s1.w;
         }
-        for (; sp < splits; ++sp) s0 += src[(size_t)sp * st];
-        gW[((size_t)co * cin_true + ci) * ksize * ksize + t] += (s0 + s1) + (s2 + s3);
+        __syncthreads();
+        {
+            const int cil = threadIdx.x & 15, ci = cit * 16 + cil;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int col = (threadIdx.x >> 4) + 16 * r, co = cot * 64 + col;
+                if (co < cout && ci < cin_true) gW[((size_t)co * cin_true + ci) * KK + t] += tile[col][cil];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+struct FinalizeLayer { const float *gacc; float *gW; int cin_true, cin, cout, ksize; };
+
+// gW[(co*cin_true + ci)*KK + t] += gacc[t][ci/4][co][ci%4]: same tile transpose as above, one source instead of `splits`;
+// blockIdx.y selects the layer (one launch for the whole net when no per-layer gradient bucket is needed)
+__global__ void __launch_bounds__(256) wgrad_finalize_kernel(const FinalizeLayer *__restrict__ table) {
+    __shared__ float tile[64][17];
+    const FinalizeLayer fl = table[blockIdx.y];
+    const float *__restrict__ gacc = fl.gacc;
+    float *__restrict__ gW = fl.gW;
+    const int cin_true = fl.cin_true, cin = fl.cin, cout = fl.cout, ksize = fl.ksize;
+    const int KK = ksize * ksize, cin4 = cin >> 2;
+    const int co_tiles = (cout + 63) >> 6, ci_tiles = cin >> 4;
+    const int ntiles = KK * co_tiles * ci_tiles;
+    const float4 *g4 = reinterpret_cast<const float4 *>(gacc);
+    for (int tl = blockIdx.x; tl < ntiles; tl += gridDim.x) {
+        const int cit = tl % ci_tiles, cot = (tl / ci_tiles) % co_tiles, t = tl / (ci_tiles * co_tiles);
+        {
+            const int col = threadIdx.x & 63, co = cot * 64 + col, c4l = threadIdx.x >> 6, c4 = cit * 4 + c4l;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (co < cout) v = __ldg(g4 + ((size_t)t * cin4 + c4) * cout + co);
+            float *tr = &tile[col][c4l * 4];
+            tr[0] = v.x; tr[1] = v.y; tr[2] = v.z; tr[3] = v.w;
+        }
+        __syncthreads();
+        {
+            const int cil = threadIdx.x & 15, ci = cit * 16 + cil;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int col = (threadIdx.x >> 4) + 16 * r, co = cot * 64 + col;
+                if (co < cout && ci < cin_true) gW[((size_t)co * cin_true + ci) * KK + t] += tile[col][cil];
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -514,7 +713,8 @@ struct HeadParams {
     float *logp, *loss_n;
     int32_t *argmax;
     bf16 *dz_out;            // dZ_{L-1}: [n][C/8][R_out][8] (NULL: forward only)
-    float *gW, *gb, *ga;     // gradient slots of the last layer
+    float *part;             // per-position partial gradients [n][9*C + 361]: weight-gradient partials, then dz of the 1-channel map
+                             // (summed over positions by head_grad_reduce_kernel: no same-address atomics from 128 CTAs)
     int n, C, R;
     int R_out, pitch_out, pad_out;
     float scale;
@@ -624,36 +824,45 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     float dzv = 0.f;
     if (valid && z > 0.f) dzv = p.scale * (expf(lp) - (pt == tgt ? 1.f : 0.f));
     dzs[rho] = dzv;
-    if (valid) atomicAdd(&p.ga[pt], dzv);                        // nn.Add gradBias (361)
-    const float dsum = block_reduce_sum(dzv, red);               // also orders the dzs writes
-    if (tid == 0) atomicAdd(p.gb, dsum);                         // conv gradBias (1)
+    float *part = p.part + (size_t)pos * (9 * p.C + DG_POINTS);
+    if (valid) part[9 * p.C + pt] = dzv;                         // nn.Add gradBias (361) and conv gradBias (1) are sums of these over positions
+    __syncthreads();                                             // orders the dzs writes
 
-    // ---- weight gradient of the last layer: gW[ci][t] += sum_rho dz[rho] * in[rho+off(t)][ci]
+    // ---- weight gradient of the last layer: gW[ci][t] = sum_rho dz[rho] * in[rho+off(t)][ci]
+    // one warp per 8-channel chunk, lanes stride over the rows (conflict-free 16-byte reads), 72 accumulators per lane,
+    // warp-shuffle reduction, one writer per element
     {
-        const int parts = blockDim.x / p.C;                      // C in {64,128,192} divides 384
-        const int ci = tid % p.C, part = tid / p.C;
-        if (part < parts) {
-            float acc[9];
+        const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
+        for (int c = warp; c < chunks; c += nwarps) {
+            float acc[9][8];
 #pragma unroll
-            for (int t = 0; t < 9; ++t) acc[t] = 0.f;
-            const uint8_t *col = img + (size_t)(ci >> 3) * p.R * 16 + (ci & 7) * 2;
-            for (int r = 21 + part; r < 400; r += parts) {
+            for (int t = 0; t < 9; ++t)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[t][e] = 0.f;
+            for (int r = 21 + lane; r < 400; r += 32) {
                 const float d = dzs[r];
                 if (d == 0.f) continue;
 #pragma unroll
                 for (int t = 0; t < 9; ++t) {
                     const int row = r + (t / 3 - 1) * 20 + (t % 3 - 1);
-                    const uint16_t hv = *reinterpret_cast<const uint16_t *>(col + (size_t)row * 16);
-                    acc[t] = fmaf(d, __uint_as_float((uint32_t)hv << 16), acc[t]);
+                    const uint4 v = *reinterpret_cast<const uint4 *>(img + ((size_t)c * p.R + row) * 16);
+                    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        acc[t][2 * e] = fmaf(d, __uint_as_float(w4[e] << 16), acc[t][2 * e]);
+                        acc[t][2 * e + 1] = fmaf(d, __uint_as_float(w4[e] & 0xFFFF0000u), acc[t][2 * e + 1]);
+                    }
                 }
             }
 #pragma unroll
-            for (int t = 0; t < 9; ++t) atomicAdd(&gws[t * p.C + ci], acc[t]);
-        }
-        __syncthreads();
-        for (int i = tid; i < 9 * p.C; i += blockDim.x) {
-            const int t = i / p.C, c = i - t * p.C;
-            atomicAdd(&p.gW[c * 9 + t], gws[i]);
+            for (int t = 0; t < 9; ++t)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float v = acc[t][e];
+#pragma unroll
+                    for (int sh = 16; sh > 0; sh >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sh);
+                    if (lane == 0) part[(c * 8 + e) * 9 + t] = v;        // Torch7 order of W[0][ci][ky][kx]
+                }
         }
     }
 
@@ -682,6 +891,33 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
             o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
             *reinterpret_cast<uint4 *>(p.dz_out + (((size_t)pos * chunks + c) * p.R_out + rho_out) * 8) = o;
         }
+    }
+}
+
+// gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order
+__global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__restrict__ part, int n, int C, float *__restrict__ gW,
+                                                               float *__restrict__ gb, float *__restrict__ ga) {
+    __shared__ float red[8];
+    const int width = 9 * C + DG_POINTS;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float s0 = 0.f, s1 = 0.f;
+    if (i < width) {
+        int k = 0;
+        for (; k + 2 <= n; k += 2) { s0 += part[(size_t)k * width + i]; s1 += part[(size_t)(k + 1) * width + i]; }
+        if (k < n) s0 += part[(size_t)k * width + i];
+    }
+    const float s = s0 + s1;
+    float bsum = 0.f;
+    if (i < 9 * C) gW[i] += s;
+    else if (i < width) { ga[i - 9 * C] += s; bsum = s; }
+#pragma unroll
+    for (int sh = 16; sh > 0; sh >>= 1) bsum += __shfl_xor_sync(0xffffffffu, bsum, sh);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = bsum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        if (t != 0.f) atomicAdd(gb, t);                // at most two blocks hold bias-gradient elements
     }
 }
 
@@ -814,10 +1050,16 @@ struct Bf16Path {
     int cin0_pad = 48;
     bf16 *x0 = nullptr;                    // [B][6][R_first][8]
     std::vector<bf16 *> h;                 // h[l], l = 1..L-1: [B][C/8][R3][8]
-    bf16 *dz[2] = {nullptr, nullptr};      // ping-pong dZ_l (3x3 geometry), l >= 2
-    bf16 *dz1 = nullptr;                   // dZ_1 in the first layer's geometry
+    std::vector<bf16 *> dzl;               // dZ of conv layer l (0-based): l = 0 in the first layer's geometry, l >= 1 in the 3x3 geometry
     std::vector<LayerOps> ops;             // per conv layer 0..L-2
+    float *head_part = nullptr;            // [B][9*C + 361] per-position partial gradients of the last layer
     PackLayer *pack_table = nullptr;       // device copy, one entry per conv layer
+    FinalizeLayer *fin_table = nullptr;    // device copy, one entry per conv layer
+    std::vector<FinalizeLayer> fin_host;
+    float *gacc = nullptr;                 // weight-gradient accumulation buffers of all conv layers (default path)
+    std::vector<size_t> gacc_off;          // per conv layer, in floats
+    size_t gacc_floats = 0;
+    bool deterministic = false;            // DG_DETERMINISTIC=1: partial tiles + ordered reduction instead of L2 reductions
     float *scratch = nullptr;              // weight-gradient partial tiles, two halves used alternately
     size_t scratch_bytes = 0;              // bytes of one half
     // the small HBM-bound gradient kernels (bias gradients, split-K reduction) run on a side stream, under the
@@ -844,7 +1086,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     dg_ctx *c = m->ctx;
     static long long *dbg = nullptr;
     static const bool timeline = getenv("DG_TIMELINE") != nullptr;
-    if (timeline && !dbg) cudaMalloc(&dbg, 148 * 10 * sizeof(long long));
+    if (timeline && !dbg) cudaMalloc(&dbg, (148 * 10 + 64) * sizeof(long long));
     cp.dbg = timeline ? dbg : nullptr;
     const size_t img_bytes = ((size_t)(cp.cin / 8) * cp.R_in * 16 + 1023) & ~(size_t)1023;
     const size_t stage = (size_t)cp.kp * cp.nb * 2;
@@ -860,7 +1102,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     }
     c->launches++;
     if (timeline) {
-        std::vector<long long> h(148 * 10);
+        std::vector<long long> h(148 * 10 + 64);
         cudaStreamSynchronize(c->stream);
         cudaMemcpy(h.data(), dbg, h.size() * 8, cudaMemcpyDeviceToHost);
         double d[7] = {0};
@@ -872,6 +1114,14 @@ static int launch_conv(dg_model *m, ConvParams cp) {
             const long long a0 = h[148 * 8 + 2 * b], a1 = h[148 * 8 + 2 * b + 1];
             t0min = std::min(t0min, a0); t0max = std::max(t0max, a0); t1max = std::max(t1max, a1); t1min = std::min(t1min, a1);
             dmax = std::max(dmax, a1 - a0); dmin = std::min(dmin, a1 - a0);
+        }
+        if (cp.nchain > 1) {
+            fprintf(stderr, "   chain (CTA 0, cycles): layer: mma-start -> all-issued | epilogue sees acc_full -> drained+handed over\n");
+            const long long t0 = h[0];
+            for (int l = 0; l < cp.nchain && l < 16; ++l)
+                fprintf(stderr, "     l=%d  mma %lld -> %lld (%lld) | epi %lld -> %lld (%lld)\n", l, h[148 * 10 + l * 4] - t0, h[148 * 10 + l * 4 + 1] - t0,
+                        h[148 * 10 + l * 4 + 1] - h[148 * 10 + l * 4], h[148 * 10 + l * 4 + 2] - t0, h[148 * 10 + l * 4 + 3] - t0,
+                        h[148 * 10 + l * 4 + 3] - h[148 * 10 + l * 4 + 2]);
         }
         fprintf(stderr, "   globaltimer ns: CTA start spread %lld, first start -> last end %lld, first end -> last end %lld, CTA duration min %lld max %lld\n",
                 t0max - t0min, t1max - t0min, t1max - t1min, dmin, dmax);
@@ -924,8 +1174,10 @@ int dg_bf16_create(dg_model *m) {
     if (int rc = alloc0((void **)&b->x0, B * img_elems(b->cin0_pad, b->g_first.rows) * 2)) return rc;
     b->h.assign(L, nullptr);
     for (int l = 1; l < L; ++l) if (int rc = alloc0((void **)&b->h[l], B * img_elems(C, DG_R3) * 2)) return rc;
-    for (int i = 0; i < 2; ++i) if (int rc = alloc0((void **)&b->dz[i], B * img_elems(C, DG_R3) * 2)) return rc;
-    if (int rc = alloc0((void **)&b->dz1, B * img_elems(C, b->g_first.rows) * 2)) return rc;
+    if (int rc = alloc0((void **)&b->head_part, B * (size_t)(9 * C + DG_POINTS) * 4)) return rc;
+    b->dzl.assign(L - 1, nullptr);
+    for (int l = 0; l < L - 1; ++l)
+        if (int rc = alloc0((void **)&b->dzl[l], B * img_elems(C, l == 0 ? b->g_first.rows : DG_R3) * 2)) return rc;
     b->ops.resize(L - 1);
     size_t scratch = 0;
     for (int l = 0; l < L - 1; ++l) {
@@ -948,10 +1200,26 @@ int dg_bf16_create(dg_model *m) {
             tab[l].wf = b->ops[l].wf; tab[l].wd = b->ops[l].wd; tab[l].ab = b->ops[l].ab;
             tab[l].cin_true = li.cin; tab[l].cin = b->ops[l].cin_pad; tab[l].cout = li.cout; tab[l].ksize = li.k;
         }
+        std::vector<FinalizeLayer> ft(L - 1);
+        size_t goff = 0;
+        for (int l = 0; l < L - 1; ++l) {
+            const LayerInfo &li = m->layers[l];
+            ft[l].gacc = nullptr; ft[l].gW = m->grads + li.offW; ft[l].cin_true = li.cin; ft[l].cin = b->ops[l].cin_pad; ft[l].cout = li.cout; ft[l].ksize = li.k;
+            (void)goff;
+        }
+        b->fin_host = ft;
+        DG_CUDA(cudaMalloc((void **)&b->fin_table, ft.size() * sizeof(FinalizeLayer)));
         DG_CUDA(cudaMalloc((void **)&b->pack_table, tab.size() * sizeof(PackLayer)));
         DG_CUDA(cudaMemcpyAsync(b->pack_table, tab.data(), tab.size() * sizeof(PackLayer), cudaMemcpyHostToDevice, st));
         DG_CUDA(cudaStreamSynchronize(st));
     }
+    b->deterministic = getenv("DG_DETERMINISTIC") != nullptr;
+    b->gacc_off.assign(L - 1, 0);
+    for (int l = 0; l < L - 1; ++l) { b->gacc_off[l] = b->gacc_floats; b->gacc_floats += (size_t)m->layers[l].k * m->layers[l].k * b->ops[l].cin_pad * m->layers[l].cout; }
+    DG_CUDA(cudaMalloc((void **)&b->gacc, b->gacc_floats * 4));
+    for (int l = 0; l < L - 1; ++l) b->fin_host[l].gacc = b->gacc + b->gacc_off[l];
+    DG_CUDA(cudaMemcpyAsync(b->fin_table, b->fin_host.data(), b->fin_host.size() * sizeof(FinalizeLayer), cudaMemcpyHostToDevice, st));
+    DG_CUDA(cudaStreamSynchronize(st));
     DG_CUDA(cudaMalloc((void **)&b->scratch, 2 * scratch));
     b->scratch_bytes = scratch;
     DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
@@ -968,10 +1236,13 @@ void dg_bf16_destroy(dg_model *m) {
     if (!b) return;
     cudaFree(b->x0);
     for (bf16 *p : b->h) if (p) cudaFree(p);
-    cudaFree(b->dz[0]); cudaFree(b->dz[1]); cudaFree(b->dz1);
+    for (bf16 *p : b->dzl) if (p) cudaFree(p);
     for (LayerOps &o : b->ops) { cudaFree(o.wf); if (o.wd) cudaFree(o.wd); cudaFree(o.ab); }
     cudaFree(b->scratch);
+    cudaFree(b->gacc);
     cudaFree(b->pack_table);
+    cudaFree(b->fin_table);
+    cudaFree(b->head_part);
     if (b->side) cudaStreamDestroy(b->side);
     delete b;
     m->bf = nullptr;
@@ -1023,8 +1294,8 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     // dZ_{L-1} lives in the geometry of layer L-1's own kernel: first-layer geometry when L-1 == 1
     const bool into_first = (m->L - 1) == 1;
     const Geom &go = into_first ? b->g_first : b->g3;
-    hp.dz_out = backward ? (into_first ? b->dz1 : b->dz[0]) : nullptr;
-    hp.gW = m->grads + li.offW; hp.gb = m->grads + li.offB; hp.ga = m->grads + li.offA;
+    hp.dz_out = backward ? b->dzl[m->L - 2] : nullptr;
+    hp.part = b->head_part;
     hp.n = m->n; hp.C = m->C; hp.R = DG_R3;
     hp.R_out = go.rows; hp.pitch_out = go.pitch; hp.pad_out = go.pad;
     hp.scale = scale;
@@ -1034,25 +1305,46 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     DG_CUDA(dg_launch_pdl(head_bf16_kernel, dim3(m->n), dim3(384), smem, c->stream, hp));
     }
     c->launches++;
+    if (backward) {
+        dg_prof_scope _ps(c, DG_K_HEAD);
+        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 255) / 256, 256, 0, c->stream>>>(b->head_part, m->n, m->C, m->grads + li.offW,
+                                                                                         m->grads + li.offB, m->grads + li.offA);
+        c->launches++;
+    }
     DG_CUDA(cudaGetLastError());
     return 0;
 }
 
+static bool chain_ok(const dg_model *m) {
+    static const bool off = getenv("DG_NO_CHAIN") != nullptr;
+    return !off && m->C <= 128 && m->L >= 4;      // one N block, one K panel, at least two C->C layers
+}
+
 int dg_bf16_forward(dg_model *m) {
     Bf16Path *b = m->bf;
-    for (int l = 0; l < m->L - 1; ++l) {
+    auto fill = [&](ConvParams &cp, int l) {
         const LayerInfo &li = m->layers[l];
         const Geom &gi = l == 0 ? b->g_first : b->g3;
-        ConvParams cp{};
         cp.in = l == 0 ? b->x0 : b->h[l];
-        cp.w = b->ops[l].wf; cp.out = b->h[l + 1]; cp.bias = b->ops[l].ab; cp.mask = nullptr;
         cp.n = m->n;
         cp.R_in = gi.rows; cp.pitch_in = gi.pitch; cp.pad_in = gi.pad; cp.ksize = li.k; cp.first = gi.first; cp.ntiles = gi.ntiles;
         cp.R_out = DG_R3; cp.pitch_out = b->g3.pitch; cp.pad_out = b->g3.pad;
         cp.R_mask = cp.pitch_mask = cp.pad_mask = 0;
         cp.mode = 0;
-        if (int rc = conv_cfg(m, cp, b->ops[l].cin_pad, li.cout)) return rc;
+    };
+    int l = 0;
+    while (l < m->L - 1) {
+        ConvParams cp{};
+        fill(cp, l);
+        int nchain = 1;
+        if (l >= 1 && chain_ok(m)) nchain = std::min(m->L - 1 - l, CONV_MAX_CHAIN);
+        for (int j = 0; j < nchain; ++j) {
+            cp.w[j] = b->ops[l + j].wf; cp.bias[j] = b->ops[l + j].ab; cp.mask[j] = nullptr; cp.out[j] = b->h[l + j + 1];
+        }
+        cp.nchain = nchain;
+        if (int rc = conv_cfg(m, cp, b->ops[l].cin_pad, m->layers[l].cout)) return rc;
         if (int rc = launch_conv(m, cp)) return rc;
+        l += nchain;
     }
     b->head_bwd_done = false;
     if (m->fused_step) return 0;          // dg_train_step: the head runs once, in dg_bf16_backward
@@ -1062,75 +1354,115 @@ int dg_bf16_forward(dg_model *m) {
 int dg_bf16_backward(dg_model *m, float scale) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
+    if (!b->deterministic) DG_CUDA(cudaMemsetAsync(b->gacc, 0, b->gacc_floats * 4, c->stream));
     if (int rc = launch_head(m, true, scale)) return rc;
     {
         const LayerInfo &lh = m->layers[m->L - 1];
         if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + lh.offW, lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS)) return rc;
     }
-    int cur = 0;                                           // dZ_{L-1} is in dz[0] (or dz1 when L-1 == 1)
-    bool rec_bias[2] = {false, false}, rec_reduce[2] = {false, false};   // events recorded in THIS pass (stream capture forbids waiting on older records)
-    for (int l = m->L - 2; l >= 0; --l) {                  // conv layer index l (0-based) = layer l+1
+    // ---- input gradients first: dZ_{l} -> dZ_{l-1} for conv layers l = L-2 .. 1 (transposed conv with flipped taps, masked by
+    // the ReLU of layer l's input h_l); with C <= 128 the whole chain is one kernel with dZ resident in shared memory
+    {
+        int l = m->L - 2;
+        while (l >= 1) {
+            ConvParams cp{};
+            cp.in = b->dzl[l];
+            cp.n = m->n;
+            cp.R_in = DG_R3; cp.pitch_in = b->g3.pitch; cp.pad_in = b->g3.pad; cp.ksize = 3; cp.first = b->g3.first; cp.ntiles = b->g3.ntiles;
+            cp.R_mask = DG_R3; cp.pitch_mask = b->g3.pitch; cp.pad_mask = b->g3.pad;
+            cp.mode = 1;
+            int nchain = chain_ok(m) ? std::min(l, CONV_MAX_CHAIN) : 1;
+            for (int j = 0; j < nchain; ++j) {
+                cp.w[j] = b->ops[l - j].wd; cp.bias[j] = nullptr; cp.mask[j] = b->h[l - j]; cp.out[j] = b->dzl[l - j - 1];
+            }
+            cp.nchain = nchain;
+            const bool into_first = (l - nchain) == 0;                 // the last output of this chain is dZ of conv layer 0
+            const Geom &go = into_first ? b->g_first : b->g3;
+            cp.R_out = go.rows; cp.pitch_out = go.pitch; cp.pad_out = go.pad;
+            if (int rc = conv_cfg(m, cp, m->layers[l].cout, m->layers[l].cin)) return rc;
+            if (int rc = launch_conv(m, cp)) return rc;
+            l -= nchain;
+        }
+    }
+    // every dZ_l is complete on the main stream: the side stream may read them
+    DG_CUDA(cudaEventRecord(b->ev_dz, c->stream));
+    DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
+    bool rec_reduce[2] = {false, false};   // events recorded in THIS pass (stream capture forbids waiting on older records)
+    static long long *wdbg = nullptr;
+    static const bool wtl = getenv("DG_TIMELINE") != nullptr;
+    if (wtl && !wdbg) cudaMalloc(&wdbg, 148 * 8 * sizeof(long long));
+    // bias gradients of every conv layer: side stream, all dZ are ready
+    for (int l = m->L - 2; l >= 0; --l) {
+        const LayerInfo &li = m->layers[l];
+        const Geom &g = l == 0 ? b->g_first : b->g3;
+        const int groups = m->n >= 64 ? 32 : (m->n >= 8 ? 8 : 1);
+        dg_prof_scope _ps(c, DG_K_BIAS_GRAD, b->side);
+        bias_grad_bf16_kernel<<<dim3(li.cout / 8, groups), 384, 0, b->side>>>(b->dzl[l], m->grads + li.offA, m->grads + li.offB, m->n, li.cout,
+                                                                             g.rows, g.pitch, g.pad, groups);
+        c->launches++;
+    }
+    // weight gradients: conv layers L-2 .. 1 have one shape and (default path) go out as ONE launch; layer 0 on its own
+    int l = m->L - 2;
+    while (l >= 0) {
         const LayerInfo &li = m->layers[l];
         const LayerOps &o = b->ops[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
-        const bf16 *dzl = l == 0 ? b->dz1 : b->dz[cur];
+        WgradPlan w;
+        if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
+        int nl = 1;
+        if (!b->deterministic && l >= 1) nl = std::min(l, WG_MAX_LAYERS);       // layers l, l-1, .., l-nl+1 (all >= 1)
         const int par = l & 1;
         float *scratch = b->scratch + (size_t)par * (b->scratch_bytes / 4);
-        // dZ_l is complete on the main stream: the side stream may read it
-        DG_CUDA(cudaEventRecord(b->ev_dz, c->stream));
-        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
-        {
-            const int groups = m->n >= 64 ? 32 : (m->n >= 8 ? 8 : 1);
-            dg_prof_scope _ps(c, DG_K_BIAS_GRAD, b->side);
-            bias_grad_bf16_kernel<<<dim3(li.cout / 8, groups), 384, 0, b->side>>>(dzl, m->grads + li.offA, m->grads + li.offB, m->n, li.cout,
-                                                                                 g.rows, g.pitch, g.pad, groups);
-            c->launches++;
+        WgradParams wp{};
+        for (int j = 0; j < nl; ++j) {
+            wp.dz[j] = b->dzl[l - j];
+            wp.x[j] = (l - j) == 0 ? b->x0 : b->h[l - j];
+            wp.gacc[j] = b->deterministic ? nullptr : b->gacc + b->gacc_off[l - j];
         }
-        DG_CUDA(cudaEventRecord(b->ev_bias[par], b->side));
-        rec_bias[par] = true;
-        {
-            WgradPlan w;
-            if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
-            WgradParams wp{};
-            wp.dz = dzl; wp.x = l == 0 ? b->x0 : b->h[l]; wp.scratch = scratch;
-            wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
-            wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
-            wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
-            // this scratch half was last read by the reduction two layers ago
-            if (rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
-            { dg_prof_scope _ps(c, DG_K_WGRAD);
-            DG_CUDA(dg_launch_pdl(wgrad_umma_kernel, dim3(w.combos * w.splits), dim3(192), w.smem, c->stream, wp));
-            }
-            c->launches++;
-            DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
-            DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));
+        wp.scratch = scratch; wp.nl = nl;
+        wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
+        wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
+        wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
+        wp.dbg = wtl ? wdbg : nullptr;
+        // deterministic path: this scratch half was last read by the reduction two layers ago
+        if (b->deterministic && rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
+        { dg_prof_scope _ps(c, DG_K_WGRAD);
+        DG_CUDA(dg_launch_pdl(wgrad_umma_kernel, dim3(w.combos * w.splits), dim3(320), w.smem, c->stream, wp));
+        }
+        c->launches++;
+        if (wp.dbg) {
+            std::vector<long long> h(148 * 8);
+            cudaStreamSynchronize(c->stream);
+            cudaMemcpy(h.data(), wp.dbg, h.size() * 8, cudaMemcpyDeviceToHost);
+            double d1 = 0, d2 = 0, d3 = 0, d4 = 0; const int gsz = w.combos * w.splits;
+            for (int i = 0; i < gsz; ++i) { d1 += (double)(h[i * 8 + 1] - h[i * 8]) / gsz; d2 += (double)(h[i * 8 + 2] - h[i * 8]) / gsz; d3 += (double)h[i * 8 + 3] / gsz; d4 += (double)(h[i * 8 + 4] - h[i * 8]) / gsz; }
+            fprintf(stderr, "wgrad timeline (cycles, mean over %d CTAs) k=%d layers=%d: mma loop start %.0f end %.0f (waiting for panels %.0f) | CTA end %.0f\n", gsz, li.k, nl, d1, d2, d3, d4);
+        }
+        DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
+        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));
+        for (int j = 0; j < nl; ++j) {
+            const int lj = l - j;
+            const LayerInfo &lij = m->layers[lj];
             { dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
-            wgrad_reduce_kernel<<<b->num_sms * 4, 256, 0, b->side>>>(scratch, m->grads + li.offW, li.cin, o.cin_pad, li.cout, li.k, w.nb,
-                                                                     w.n_mblk, w.n_nblk, w.splits);
+            if (b->deterministic)
+                wgrad_reduce_kernel<<<b->num_sms * 8, 256, 0, b->side>>>(scratch, m->grads + lij.offW, lij.cin, b->ops[lj].cin_pad, lij.cout, lij.k, w.nb,
+                                                                         w.n_mblk, w.n_nblk, w.splits);
+            else if (c->world > 1)     // per-layer so that the layer's gradient bucket can leave while the rest is still computed
+                wgrad_finalize_kernel<<<dim3(b->num_sms, 1), 256, 0, b->side>>>(b->fin_table + lj);
             }
-            c->launches++;
-            DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
-            rec_reduce[par] = true;
+            if (b->deterministic || c->world > 1) c->launches++;
+            // the layer's gradient slice is final once the side stream has run both of its kernels
+            if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + lij.offW, lij.nW + lij.cout + (size_t)lij.cout * DG_POINTS, b->side)) return rc;
         }
-        // the layer's gradient slice is final once the side stream has run both kernels
-        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + li.offW, li.nW + li.cout + (size_t)li.cout * DG_POINTS, b->side)) return rc;
-        // the next dgrad overwrites the dZ buffer that the bias-gradient kernel of the layer above was reading
-        if (rec_bias[par ^ 1]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_bias[par ^ 1], 0));
-        if (l >= 1) {
-            // dZ_{l} -> dZ_{l-1}: transposed conv with flipped taps, masked by ReLU of layer l's input h_l
-            const bool into_first = (l - 1) == 0;
-            const Geom &go = into_first ? b->g_first : b->g3;
-            ConvParams cp{};
-            cp.in = dzl; cp.w = o.wd; cp.out = into_first ? b->dz1 : b->dz[cur ^ 1]; cp.bias = nullptr; cp.mask = b->h[l];
-            cp.n = m->n;
-            cp.R_in = DG_R3; cp.pitch_in = b->g3.pitch; cp.pad_in = b->g3.pad; cp.ksize = 3; cp.first = b->g3.first; cp.ntiles = b->g3.ntiles;
-            cp.R_out = go.rows; cp.pitch_out = go.pitch; cp.pad_out = go.pad;
-            cp.R_mask = DG_R3; cp.pitch_mask = b->g3.pitch; cp.pad_mask = b->g3.pad;
-            cp.mode = 1;
-            if (int rc = conv_cfg(m, cp, li.cout, li.cin)) return rc;
-            if (int rc = launch_conv(m, cp)) return rc;
-            cur ^= 1;
-        }
+        DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
+        rec_reduce[par] = true;
+        l -= nl;
+    }
+    if (!b->deterministic && c->world == 1) {
+        // single GPU: one launch folds every layer's accumulation buffer into the Torch7-order gradient
+        dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
+        wgrad_finalize_kernel<<<dim3(48, m->L - 1), 256, 0, b->side>>>(b->fin_table);
+        c->launches++;
     }
     DG_CUDA(cudaEventRecord(b->ev_join, b->side));
     DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_join, 0));
