@@ -313,16 +313,46 @@ __global__ void __launch_bounds__(32) board_ladders_kernel(const uint8_t *__rest
     for (int i = lane; i < 2 * DG_POINTS; i += 32) o[i] = (uint8_t)((&key[0][0])[i] & 255);
 }
 
+// update_board (makedata.lua:329-354): every age in 1..254 grows by one, the stone is placed, captured groups (and the
+// own group on suicide) are removed, and every point whose state the move set gets age 1.  One CTA per board.
+__global__ void __launch_bounds__(384) update_boards_kernel(uint8_t *__restrict__ stones, uint8_t *__restrict__ age, const uint8_t *__restrict__ mx,
+                                                            const uint8_t *__restrict__ my, const uint8_t *__restrict__ mplayer, int *__restrict__ status) {
+    __shared__ uint32_t before[2][NW], after[2][NW];
+    const int b = blockIdx.x, h = threadIdx.x;
+    uint8_t *s = stones + (size_t)b * DG_POINTS, *a = age + (size_t)b * DG_POINTS;
+    const int move = (mx[b] - 1) * DG_BOARD + (my[b] - 1), player = mplayer[b];
+    if (h < 2 * NW) (&before[0][0])[h] = 0;
+    __syncthreads();
+    const int c = h < DG_POINTS ? s[h] : 0;
+    if (c == 1 || c == 2) atomicOr(&before[c - 1][h >> 5], 1u << (h & 31));
+    __syncthreads();
+    if (h == 0) {
+        if (s[move] != 0) {
+            status[b] = 1;                                  // "playing somewhere that's already been played!" (makedata.lua:352)
+            for (int i = 0; i < NW; ++i) { after[0][i] = before[0][i]; after[1][i] = before[1][i]; }
+        } else {
+            status[b] = 0;
+            BB mine, theirs;
+            for (int i = 0; i < NW; ++i) { mine.w[i] = before[player - 1][i]; theirs.w[i] = before[2 - player][i]; }
+            bb_play(mine, theirs, move);
+            for (int i = 0; i < NW; ++i) { after[player - 1][i] = mine.w[i]; after[2 - player][i] = theirs.w[i]; }
+        }
+    }
+    __syncthreads();
+    if (h < DG_POINTS && status[b] == 0) {
+        const int nb = ((after[0][h >> 5] >> (h & 31)) & 1u) ? 1 : (((after[1][h >> 5] >> (h & 31)) & 1u) ? 2 : 0);
+        int ag = a[h];
+        if (ag > 0 && ag < 255) ag++;
+        // set() is called for the placed stone and for every removed stone (also the placed stone itself on suicide)
+        if (nb != c || h == move) ag = 1;
+        s[h] = (uint8_t)nb;
+        a[h] = (uint8_t)ag;
+    }
+}
+
 static bool g_consts_set[64] = {false};
 
-extern "C" int dg_summarize_boards(dg_ctx *c, const uint8_t *stones, uint8_t *out, int n) {
-    DG_REQUIRE(c, "dg_summarize_boards: ctx is NULL");
-    DG_REQUIRE(n >= 0, "dg_summarize_boards: n < 0");
-    if (n == 0) return 0;
-    DG_REQUIRE(stones && out, "dg_summarize_boards: NULL buffer");
-    for (size_t i = 0; i < (size_t)n * DG_POINTS; ++i)
-        DG_REQUIRE(stones[i] <= 2, "dg_summarize_boards: board %zu has a point value %d outside {0,1,2}", i / DG_POINTS, stones[i]);
-    DG_CUDA(cudaSetDevice(c->dev));
+static int board_consts(dg_ctx *c) {
     if (!g_consts_set[c->dev & 63]) {
         uint32_t c0[NW] = {0}, c18[NW] = {0};
         for (int x = 0; x < DG_BOARD; ++x) {
@@ -334,6 +364,52 @@ extern "C" int dg_summarize_boards(dg_ctx *c, const uint8_t *stones, uint8_t *ou
         DG_CUDA(cudaMemcpyToSymbol(c_col18, c18, sizeof c18));
         g_consts_set[c->dev & 63] = true;
     }
+    return 0;
+}
+
+extern "C" int dg_update_boards(dg_ctx *c, uint8_t *stones, uint8_t *age, const uint8_t *x, const uint8_t *y, const uint8_t *player, int n) {
+    DG_REQUIRE(c, "dg_update_boards: ctx is NULL");
+    DG_REQUIRE(n >= 0, "dg_update_boards: n < 0");
+    if (n == 0) return 0;
+    DG_REQUIRE(stones && age && x && y && player, "dg_update_boards: NULL buffer");
+    for (int i = 0; i < n; ++i) {
+        DG_REQUIRE(x[i] >= 1 && x[i] <= 19 && y[i] >= 1 && y[i] <= 19, "move %d: (%d,%d) outside the board", i, x[i], y[i]);
+        DG_REQUIRE(player[i] == 1 || player[i] == 2, "move %d: player %d not in {1,2}", i, player[i]);
+    }
+    DG_CUDA(cudaSetDevice(c->dev));
+    if (int rc = board_consts(c)) return rc;
+    const size_t bb = (size_t)n * DG_POINTS;
+    const size_t off_age = (bb + 255) / 256 * 256, off_m = off_age + (bb + 255) / 256 * 256, off_st = (off_m + 3 * (size_t)n + 255) / 256 * 256;
+    char *d = nullptr;
+    if (int rc = dg_ctx_scratch(c, off_st + (size_t)n * 4, (void **)&d)) return rc;
+    DG_CUDA(cudaMemcpyAsync(d, stones, bb, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(d + off_age, age, bb, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(d + off_m, x, n, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(d + off_m + n, y, n, cudaMemcpyHostToDevice, c->stream));
+    DG_CUDA(cudaMemcpyAsync(d + off_m + 2 * (size_t)n, player, n, cudaMemcpyHostToDevice, c->stream));
+    update_boards_kernel<<<n, 384, 0, c->stream>>>((uint8_t *)d, (uint8_t *)d + off_age, (const uint8_t *)d + off_m, (const uint8_t *)d + off_m + n,
+                                                   (const uint8_t *)d + off_m + 2 * (size_t)n, (int *)(d + off_st));
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    std::vector<int> st(n);
+    DG_CUDA(cudaMemcpyAsync(stones, d, bb, cudaMemcpyDeviceToHost, c->stream));
+    DG_CUDA(cudaMemcpyAsync(age, d + off_age, bb, cudaMemcpyDeviceToHost, c->stream));
+    DG_CUDA(cudaMemcpyAsync(st.data(), d + off_st, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < n; ++i)
+        DG_REQUIRE(st[i] == 0, "dg_update_boards: board %d: playing somewhere that's already been played (makedata.lua:352); that board is left unchanged", i);
+    return 0;
+}
+
+extern "C" int dg_summarize_boards(dg_ctx *c, const uint8_t *stones, uint8_t *out, int n) {
+    DG_REQUIRE(c, "dg_summarize_boards: ctx is NULL");
+    DG_REQUIRE(n >= 0, "dg_summarize_boards: n < 0");
+    if (n == 0) return 0;
+    DG_REQUIRE(stones && out, "dg_summarize_boards: NULL buffer");
+    for (size_t i = 0; i < (size_t)n * DG_POINTS; ++i)
+        DG_REQUIRE(stones[i] <= 2, "dg_summarize_boards: board %zu has a point value %d outside {0,1,2}", i / DG_POINTS, stones[i]);
+    DG_CUDA(cudaSetDevice(c->dev));
+    if (int rc = board_consts(c)) return rc;
     const size_t in_b = (size_t)n * DG_POINTS, out_b = (size_t)n * 7 * DG_POINTS;
     const size_t off_out = (in_b + 255) / 256 * 256;
     const size_t off_list = (off_out + out_b + 255) / 256 * 256;

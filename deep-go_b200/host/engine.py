@@ -104,6 +104,16 @@ class Context:
         return out
 
 
+def _update_boards(self, stones, age, x, y, player):
+    """dg_update_boards: in-place update_board (makedata.lua:329-354) of n boards; x, y 1-based."""
+    assert stones.dtype == np.uint8 and age.dtype == np.uint8 and stones.flags.c_contiguous and age.flags.c_contiguous
+    xa, xp = _u8(x); ya, yp = _u8(y); pa, pp = _u8(player)
+    check(self.L.dg_update_boards(self.h, ffi.cast("uint8_t *", stones.ctypes.data), ffi.cast("uint8_t *", age.ctypes.data), xp, yp, pp, len(xa)))
+
+
+Context.update_boards = _update_boards
+
+
 def dp_unique_id():
     buf = bytearray(128)
     check(_dg.lib().dg_dp_unique_id(ffi.from_buffer(buf)))

@@ -107,6 +107,11 @@ int dg_t7_read_record(const char *path, uint8_t *raw, int *x, int *y, int *playe
 /* summarize_board (makedata.lua:143-153): stones u8[n][19][19] in {0,1,2} ->
  * out u8[n][7][19][19]: liberties, liberties_after[p=1,2], kills[p=1,2], ladders[p=1,2]. */
 int dg_summarize_boards(dg_ctx *ctx, const uint8_t *stones, uint8_t *out, int n);
+/* update_board (makedata.lua:329-354) for n independent boards, in place: ages 1..254 grow by one, the stone
+ * (x,y 1-based, player in {1,2}) is placed, captured groups and, on suicide, the own group are removed, and every
+ * point the move set gets age 1.  An occupied target is an error (makedata.lua:352); that board is left unchanged. */
+int dg_update_boards(dg_ctx *ctx, uint8_t *stones, uint8_t *age, const uint8_t *x, const uint8_t *y,
+                     const uint8_t *player, int n);
 
 /* ---- model (experiments.lua:133-153 getBasicModel + :105-107 getParameters) ---------------- */
 /* numLayers x [pad, conv k, +b[c], +a[c,x,y], ReLU] + log-softmax(361); kernels {kFirst,3,3,..},

@@ -57,3 +57,27 @@ def test_edge_cases():
     assert ctx.summarize_boards(empty[:0]).shape == (0, 7, 19, 19)
     with pytest.raises(deepgo_b200.DeepGoError):
         ctx.summarize_boards(np.full((1, 19, 19), 3, np.uint8))
+
+
+def test_update_boards_replays_every_successor(golden):
+    """all 4,376 (record, next record) pairs of the corpus: stones and age after the labelled move, bit-exact"""
+    raw, game, move = golden["raw"], golden["game"], golden["move"]
+    idx = np.array([i for i in range(len(raw) - 1) if game[i + 1] == game[i] and move[i + 1] == move[i] + 1])
+    stones = np.ascontiguousarray(raw[idx, 0]); age = np.ascontiguousarray(raw[idx, 6])
+    U.ctx().update_boards(stones, age, golden["x"][idx], golden["y"][idx], golden["player"][idx])
+    assert len(idx) == 4376
+    assert np.array_equal(stones, raw[idx + 1, 0]) and np.array_equal(age, raw[idx + 1, 6])
+
+
+def test_update_boards_suicide_and_occupied():
+    import deepgo_b200
+    from oracle import board
+    s = np.zeros((1, 19, 19), np.uint8); a = np.zeros((1, 19, 19), np.uint8)
+    s[0, 0, 1] = 1; s[0, 1, 0] = 1; a[0, 0, 1] = 254; a[0, 1, 0] = 255
+    s2, a2 = s[0].copy(), a[0].copy()
+    board.update_board(s2, a2, 0, 0, 2)                      # white plays the corner: suicide
+    U.ctx().update_boards(s, a, [1], [1], [2])
+    assert np.array_equal(s[0], s2) and np.array_equal(a[0], a2)
+    assert a[0, 0, 0] == 1 and a[0, 0, 1] == 255 and a[0, 1, 0] == 255 and s[0, 0, 0] == 0
+    with pytest.raises(deepgo_b200.DeepGoError, match="already been played"):
+        U.ctx().update_boards(s, a, [1], [2], [2])

