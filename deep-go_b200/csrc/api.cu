@@ -437,9 +437,8 @@ extern "C" int dg_loss_backward(dg_model *m, float *loss_out) {
 extern "C" int dg_sgd_step(dg_model *m, float rate) {
     DG_REQUIRE(m, "dg_sgd_step: model is NULL");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
-    if (int rc = dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate)) return rc;
-    if (m->bf) return dg_bf16_params_changed(m);
-    return 0;
+    if (m->bf) return dg_bf16_sgd_step(m, rate, nullptr);
+    return dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate);
 }
 
 // one fused step on the context's stream: eval() of train.lua:4-12 followed by SGD:step (train.lua:131)
@@ -452,10 +451,7 @@ static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
     m->fused_step = false;
     if (rc) return rc;
     if (int rc2 = dg_dp_finish(c)) return rc2;                             // buckets were issued layer by layer in backward
-    if (rate_from_device) {
-        if (int rc2 = dg_launch_sgd_dev_rate(c, m->params, m->grads, m->P, m->d_rate)) return rc2;
-        return dg_bf16_params_changed(m);
-    }
+    if (rate_from_device) return dg_bf16_sgd_step(m, rate, m->d_rate);
     return dg_sgd_step(m, rate);                                           // train.lua:131
 }
 

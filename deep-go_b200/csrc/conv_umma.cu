@@ -713,6 +713,7 @@ struct HeadParams {
     float *logp, *loss_n;
     int32_t *argmax;
     bf16 *dz_out;            // dZ_{L-1}: [n][C/8][R_out][8] (NULL: forward only)
+    long long *dbg;          // optional phase timestamps (DG_TIMELINE=1)
     float *part;             // per-position partial gradients [n][9*C + 361]: weight-gradient partials, then dz of the 1-channel map
                              // (summed over positions by head_grad_reduce_kernel: no same-address atomics from 128 CTAs)
     int n, C, R;
@@ -748,6 +749,8 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     __shared__ int redi[12];
     __shared__ float dzs[DG_R3 + 32];            // dz of the 1-channel map by image row, zero at pads
     const int pos = blockIdx.x, tid = threadIdx.x;
+#define HSTAMP(k) do { if (p.dbg && tid == 0) p.dbg[blockIdx.x * 8 + (k)] = clock64(); } while (0)
+    HSTAMP(0);
     const int chunks = p.C >> 3;
     const uint32_t img_bytes = (uint32_t)chunks * p.R * 16;
     uint8_t *img = smem;
@@ -771,6 +774,7 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     for (int i = tid; i < DG_R3 + 32; i += blockDim.x) dzs[i] = 0.f;
     __syncthreads();
     mbar_wait(&bar, 0);
+    HSTAMP(1);
 
     // ---- forward: one thread per image row 21..404
     const int rho = 21 + tid;
@@ -786,16 +790,17 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
             const float *wt = ws + t * p.C;
             for (int c = 0; c < chunks; ++c) {
                 const uint4 v = *reinterpret_cast<const uint4 *>(img + ((size_t)c * p.R + row) * 16);
-                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    acc = fmaf(__uint_as_float(w4[e] << 16), wt[c * 8 + 2 * e], acc);
-                    acc = fmaf(__uint_as_float(w4[e] & 0xFFFF0000u), wt[c * 8 + 2 * e + 1], acc);
-                }
+                // weights as two 16-byte broadcast loads per chunk (the loop is shared-memory-instruction bound)
+                const float4 wa = *reinterpret_cast<const float4 *>(wt + c * 8), wb = *reinterpret_cast<const float4 *>(wt + c * 8 + 4);
+                acc = fmaf(__uint_as_float(v.x << 16), wa.x, acc); acc = fmaf(__uint_as_float(v.x & 0xFFFF0000u), wa.y, acc);
+                acc = fmaf(__uint_as_float(v.y << 16), wa.z, acc); acc = fmaf(__uint_as_float(v.y & 0xFFFF0000u), wa.w, acc);
+                acc = fmaf(__uint_as_float(v.z << 16), wb.x, acc); acc = fmaf(__uint_as_float(v.z & 0xFFFF0000u), wb.y, acc);
+                acc = fmaf(__uint_as_float(v.w << 16), wb.z, acc); acc = fmaf(__uint_as_float(v.w & 0xFFFF0000u), wb.w, acc);
             }
         }
         z = acc + p.b[0] + p.a[pt];
     }
+    HSTAMP(2);
     const float h = valid ? fmaxf(z, 0.f) : -INFINITY;           // ReLU stays before LogSoftMax (experiments.lua:147)
     const float mx = block_reduce_max(h, red);
     const float se = block_reduce_sum(valid ? expf(h - mx) : 0.f, red);
@@ -818,6 +823,7 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     }
     const int tgt = p.targets ? p.targets[pos] : -1;
     if (valid && pt == tgt && p.loss_n) p.loss_n[pos] = -lp;
+    HSTAMP(3);
     if (!p.dz_out) return;
 
     // ---- backward of LogSoftMax + NLL + ReLU on the 1-channel map
@@ -866,6 +872,8 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
         }
     }
 
+    __syncthreads();
+    HSTAMP(4);
     // ---- input gradient + ReLU mask of layer L-1: dZ[rho][c] = (in[rho][c] > 0) * sum_t dz[rho - off(t)] * W[c][t]
     if (valid) {
         float d9[9];
@@ -877,12 +885,17 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
             const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
             float v[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                float s = 0.f;
+            for (int e = 0; e < 8; ++e) v[e] = 0.f;
 #pragma unroll
-                for (int t = 0; t < 9; ++t) s = fmaf(d9[t], ws[t * p.C + c * 8 + e], s);
+            for (int t = 0; t < 9; ++t) {
+                const float4 wa = *reinterpret_cast<const float4 *>(ws + t * p.C + c * 8), wb = *reinterpret_cast<const float4 *>(ws + t * p.C + c * 8 + 4);
+                v[0] = fmaf(d9[t], wa.x, v[0]); v[1] = fmaf(d9[t], wa.y, v[1]); v[2] = fmaf(d9[t], wa.z, v[2]); v[3] = fmaf(d9[t], wa.w, v[3]);
+                v[4] = fmaf(d9[t], wb.x, v[4]); v[5] = fmaf(d9[t], wb.y, v[5]); v[6] = fmaf(d9[t], wb.z, v[6]); v[7] = fmaf(d9[t], wb.w, v[7]);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
                 const uint32_t hh = (hw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
-                v[e] = (hh != 0 && (hh & 0x8000u) == 0) ? s : 0.f;
+                if (!(hh != 0 && (hh & 0x8000u) == 0)) v[e] = 0.f;
             }
             uint4 o;
             __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
@@ -892,6 +905,7 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
             *reinterpret_cast<uint4 *>(p.dz_out + (((size_t)pos * chunks + c) * p.R_out + rho_out) * 8) = o;
         }
     }
+    HSTAMP(5);
 }
 
 // gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order
@@ -1036,6 +1050,87 @@ __global__ void __launch_bounds__(256) pack_layer_kernel(const PackLayer *__rest
     }
 }
 
+// SGD:step (optimizer.lua:25) fused with the operand repack: block (x = group of 8 output channels, y = conv layer) reads its
+// 8 master weight rows and their gradients coalesced, writes p <- p + (-rate)*g back, and emits the bf16 operands from shared
+// memory: forward copy as 128-byte runs (8 co x 8 ci), input-gradient copy as contiguous 16-byte (8 co) entries per ci, and
+// the fp32 epilogue bias b[c] + a[c][x][y].  The 1-channel last layer (y = gridDim.y - 1) only gets the plain update.
+struct SgdPackLayer {
+    float *W, *b, *a;            // master parameters of the layer (Torch7 order)
+    const float *gW, *gb, *ga;   // gradients
+    bf16 *wf, *wd;
+    float *ab;
+    int cin_true, cin, cout, ksize;
+};
+
+__global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__restrict__ table, float rate, const float *__restrict__ rate_dev,
+                                                       int R_out, int pitch_out, int pad_out, int smem_row) {
+    extern __shared__ float wrow[];                 // [8][smem_row]: the 8 updated weight rows
+    __shared__ float bnew[8];
+    dg_pdl_launch_dependents();
+    dg_pdl_wait();
+    const SgdPackLayer L = table[blockIdx.y];
+    const float neg_rate = -(rate_dev ? *rate_dev : rate);
+    const int KK = L.ksize * L.ksize, row = L.cin_true * KK;
+    const int co0 = blockIdx.x * 8;
+    if (co0 >= L.cout) return;
+    const int nco = min(8, L.cout - co0);
+    // ---- weights: update in place, keep the new values in shared memory
+    // the 8 rows are contiguous in the master vector: a flat, coalesced, unrolled sweep (few threads: keep loads in flight)
+    {
+        float *Wp = L.W + (size_t)co0 * row;
+        const float *Gp = L.gW + (size_t)co0 * row;
+        const int total = nco * row;
+#pragma unroll 4
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const float v = fmaf(neg_rate, __ldg(Gp + i), Wp[i]);
+            Wp[i] = v;
+            if (L.wf) { const int r = i / row; wrow[r * smem_row + (i - r * row)] = v; }
+        }
+    }
+    if (threadIdx.x < nco) {
+        const float v = fmaf(neg_rate, L.gb[co0 + threadIdx.x], L.b[co0 + threadIdx.x]);
+        L.b[co0 + threadIdx.x] = v;
+        bnew[threadIdx.x] = v;
+    }
+    __syncthreads();
+    // ---- per-point bias: update, and emit b + a in the blocked epilogue layout (32 contiguous bytes per point)
+    for (int i = threadIdx.x; i < nco * DG_POINTS; i += blockDim.x) {
+        const int r = i / DG_POINTS, pt = i - r * DG_POINTS;
+        const size_t gi = (size_t)(co0 + r) * DG_POINTS + pt;
+        const float v = fmaf(neg_rate, L.ga[gi], L.a[gi]);
+        L.a[gi] = v;
+        if (L.ab) {
+            const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
+            const int rho = (x + pad_out) * pitch_out + y + pad_out;
+            L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + r] = v + bnew[r];
+        }
+    }
+    if (!L.wf) return;
+    // ---- forward operand wf[t][ci/8][co][8]: one thread per (t, ci8, r) writes 8 ci = 16 bytes; r fastest -> 128-byte runs
+    const int cin8 = L.cin >> 3;
+    for (int i = threadIdx.x; i < KK * cin8 * 8; i += blockDim.x) {
+        const int r = i & 7, c8 = (i >> 3) % cin8, t = i / (8 * cin8);
+        if (r >= nco) continue;
+        __align__(16) bf16 v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int ci = c8 * 8 + e;
+            v[e] = __float2bfloat16(ci < L.cin_true ? wrow[r * smem_row + ci * KK + t] : 0.f);
+        }
+        *reinterpret_cast<uint4 *>(L.wf + (((size_t)t * cin8 + c8) * L.cout + co0 + r) * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+    // ---- input-gradient operand wd[t'][co/8][ci][8] = W[co][ci][KK-1-t']: one thread per (t', ci) writes the 8 co of this block
+    if (L.wd && nco == 8) {
+        for (int i = threadIdx.x; i < KK * L.cin; i += blockDim.x) {
+            const int ci = i % L.cin, t = i / L.cin;
+            __align__(16) bf16 v[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) v[r] = __float2bfloat16(ci < L.cin_true ? wrow[r * smem_row + ci * KK + (KK - 1 - t)] : 0.f);
+            *reinterpret_cast<uint4 *>(L.wd + (((size_t)t * (L.cout >> 3) + (co0 >> 3)) * L.cin + ci) * 8) = *reinterpret_cast<const uint4 *>(v);
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -1055,6 +1150,8 @@ struct Bf16Path {
     float *head_part = nullptr;            // [B][9*C + 361] per-position partial gradients of the last layer
     PackLayer *pack_table = nullptr;       // device copy, one entry per conv layer
     FinalizeLayer *fin_table = nullptr;    // device copy, one entry per conv layer
+    SgdPackLayer *sgd_table = nullptr;     // device copy, one entry per layer (the 1-channel last layer included)
+    int sgd_smem_row = 0, sgd_max_co8 = 0;
     std::vector<FinalizeLayer> fin_host;
     float *gacc = nullptr;                 // weight-gradient accumulation buffers of all conv layers (default path)
     std::vector<size_t> gacc_off;          // per conv layer, in floats
@@ -1208,6 +1305,19 @@ int dg_bf16_create(dg_model *m) {
             (void)goff;
         }
         b->fin_host = ft;
+        std::vector<SgdPackLayer> sg(L);
+        for (int l = 0; l < L; ++l) {
+            const LayerInfo &li = m->layers[l];
+            sg[l].W = m->params + li.offW; sg[l].b = m->params + li.offB; sg[l].a = m->params + li.offA;
+            sg[l].gW = m->grads + li.offW; sg[l].gb = m->grads + li.offB; sg[l].ga = m->grads + li.offA;
+            sg[l].wf = l < L - 1 ? b->ops[l].wf : nullptr; sg[l].wd = l < L - 1 ? b->ops[l].wd : nullptr; sg[l].ab = l < L - 1 ? b->ops[l].ab : nullptr;
+            sg[l].cin_true = li.cin; sg[l].cin = l < L - 1 ? b->ops[l].cin_pad : li.cin; sg[l].cout = li.cout; sg[l].ksize = li.k;
+            b->sgd_smem_row = std::max(b->sgd_smem_row, li.cin * li.k * li.k + 1);
+            b->sgd_max_co8 = std::max(b->sgd_max_co8, (li.cout + 7) / 8);
+        }
+        DG_CUDA(cudaMalloc((void **)&b->sgd_table, sg.size() * sizeof(SgdPackLayer)));
+        DG_CUDA(cudaMemcpyAsync(b->sgd_table, sg.data(), sg.size() * sizeof(SgdPackLayer), cudaMemcpyHostToDevice, st));
+        DG_CUDA(cudaFuncSetAttribute(sgd_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * b->sgd_smem_row * 4));
         DG_CUDA(cudaMalloc((void **)&b->fin_table, ft.size() * sizeof(FinalizeLayer)));
         DG_CUDA(cudaMalloc((void **)&b->pack_table, tab.size() * sizeof(PackLayer)));
         DG_CUDA(cudaMemcpyAsync(b->pack_table, tab.data(), tab.size() * sizeof(PackLayer), cudaMemcpyHostToDevice, st));
@@ -1242,6 +1352,7 @@ void dg_bf16_destroy(dg_model *m) {
     cudaFree(b->gacc);
     cudaFree(b->pack_table);
     cudaFree(b->fin_table);
+    cudaFree(b->sgd_table);
     cudaFree(b->head_part);
     if (b->side) cudaStreamDestroy(b->side);
     delete b;
@@ -1254,6 +1365,20 @@ int dg_bf16_params_changed(dg_model *m) {
     {
         dg_prof_scope _ps(c, DG_K_PACK);
         DG_CUDA(dg_launch_pdl(pack_layer_kernel, dim3(b->num_sms, m->L - 1), dim3(256), 0, c->stream, (const PackLayer *)b->pack_table, (int)DG_R3, b->g3.pitch, b->g3.pad));
+    }
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// SGD update + operand repack in one launch; rate_dev != NULL: the rate is read from device memory (captured graph)
+int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    {
+        dg_prof_scope _ps(c, DG_K_SGD);
+        DG_CUDA(dg_launch_pdl(sgd_pack_kernel, dim3(b->sgd_max_co8, m->L), dim3(1024), (size_t)8 * b->sgd_smem_row * 4, c->stream,
+                              (const SgdPackLayer *)b->sgd_table, rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
@@ -1296,6 +1421,10 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     const Geom &go = into_first ? b->g_first : b->g3;
     hp.dz_out = backward ? b->dzl[m->L - 2] : nullptr;
     hp.part = b->head_part;
+    static long long *hdbg = nullptr;
+    static const bool htl = getenv("DG_TIMELINE") != nullptr;
+    if (htl && !hdbg) cudaMalloc(&hdbg, 4096 * 8 * sizeof(long long));
+    hp.dbg = htl && m->n <= 4096 ? hdbg : nullptr;
     hp.n = m->n; hp.C = m->C; hp.R = DG_R3;
     hp.R_out = go.rows; hp.pitch_out = go.pitch; hp.pad_out = go.pad;
     hp.scale = scale;
@@ -1305,6 +1434,14 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     DG_CUDA(dg_launch_pdl(head_bf16_kernel, dim3(m->n), dim3(384), smem, c->stream, hp));
     }
     c->launches++;
+    if (hp.dbg && backward) {
+        std::vector<long long> h((size_t)m->n * 8);
+        cudaStreamSynchronize(c->stream);
+        cudaMemcpy(h.data(), hp.dbg, h.size() * 8, cudaMemcpyDeviceToHost);
+        double d[6] = {0};
+        for (int i = 0; i < m->n; ++i) for (int k = 1; k < 6; ++k) d[k] += (double)(h[i * 8 + k] - h[i * 8]) / m->n;
+        fprintf(stderr, "head timeline (cycles, mean over %d CTAs): image %.0f | logits %.0f | softmax %.0f | weight grad %.0f | input grad %.0f\n", m->n, d[1], d[2], d[3], d[4], d[5]);
+    }
     if (backward) {
         dg_prof_scope _ps(c, DG_K_HEAD);
         head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 255) / 256, 256, 0, c->stream>>>(b->head_part, m->n, m->C, m->grads + li.offW,

@@ -34,7 +34,8 @@ struct dg_model {
 // conv_umma.cu
 int dg_bf16_create(dg_model *m);
 void dg_bf16_destroy(dg_model *m);
-int dg_bf16_params_changed(dg_model *m);                 // refresh bf16 operand copies from the fp32 master
+int dg_bf16_params_changed(dg_model *m);
+int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev);   // fused SGD update + operand repack                 // refresh bf16 operand copies from the fp32 master
 int dg_bf16_stage_planes(dg_model *m);                   // act[0] (fp32 NCHW) -> blocked bf16 input image
 int dg_bf16_stage_raw(dg_model *m);                      // raw records -> blocked bf16 input image
 int dg_bf16_forward(dg_model *m);                        // fills m->d_logp-ready logits via head
