@@ -278,6 +278,12 @@ def run_ours(args, rank, local_rank, world):
 
 
 def main():
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL prints its version banner to stdout)
+    # is sent to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)

@@ -462,7 +462,9 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     DG_REQUIRE(m->have_targets, "dg_train_step: the staged batch has no targets");
     DG_REQUIRE(m->n > 0, "dg_train_step: no batch staged");
     static const bool no_graph = getenv("DG_NO_GRAPH") != nullptr || getenv("DG_TIMELINE") != nullptr;
-    const bool use_graph = m->prec == DG_PREC_BF16 && c->world == 1 && !c->prof_on && !no_graph;
+    // with data parallelism the NCCL allreduce is captured too (the communication stream joins the capture through events)
+    static const bool no_dp_graph = getenv("DG_NO_DP_GRAPH") != nullptr;
+    const bool use_graph = m->prec == DG_PREC_BF16 && (c->world == 1 || !no_dp_graph) && !c->prof_on && !no_graph;
     if (use_graph) {
         // the ~50 launches and the cross-stream event edges of a step are captured once per batch size and replayed
         *m->h_rate = rate;
