@@ -85,6 +85,19 @@ static inline cudaError_t dg_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim
     cfg.attrs = at; cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
+// same, as thread-block clusters of `cluster` CTAs along x (grid.x must be a multiple of it)
+template <typename KArg, typename Arg>
+static inline cudaError_t dg_launch_pdl(void (*kernel)(KArg), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Arg arg, int cluster) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = cluster; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 2;
+    return cudaLaunchKernelEx(&cfg, kernel, KArg(arg));
+}
 #endif
 
 // per-kernel CUDA-event timing (dg_prof_*): brackets one launch on the context's stream when enabled

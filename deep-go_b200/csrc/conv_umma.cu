@@ -44,7 +44,7 @@ struct ConvParams {
     // nchain > 1 needs cin == cout <= 128 (one N block, one K panel) and the 3x3 geometry in and out.
     const bf16 *w[CONV_MAX_CHAIN];     // [taps][cin/8][cout][8]
     bf16 *out[CONV_MAX_CHAIN];         // [n][cout/8][R_out][8]   every layer's output also goes to HBM (backward needs it)
-    const float *bias[CONV_MAX_CHAIN]; // mode 0: [cout/8][R_out][8] fp32, b[c] + a[c][x][y]
+    const bf16 *bias[CONV_MAX_CHAIN];  // mode 0: [cout/8][R_out][8] bf16, b[c] + a[c][x][y] (16 bytes per row and channel chunk)
     const bf16 *mask[CONV_MAX_CHAIN];  // mode 1: [n][cout/8][R_mask][8], output kept where mask > 0
     int nchain;
     int n, cin, cout;
@@ -64,36 +64,51 @@ __device__ __forceinline__ long long dg_globaltimer() { long long t; asm volatil
 #define CONV_MAX_STAGES 8
 #define CONV_MAX_KPANELS 4
 
-__global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant__ ConvParams p) {
+// PAIR = true: two CTAs of a cluster (two SMs of a TPC) work as one cta_group::2 unit.  Each CTA holds ITS position's image
+// (its 128-row halves of the M = 256 MMA) and HALF of every weight stage (64 of the 128 output channels); the leader CTA
+// issues the MMAs for both, the tensor cores share the weight halves.  Per SM that halves the weight bytes written into and
+// read out of shared memory -- the bandwidth that bounds the single-CTA kernel (87 instead of 65 cycles per MMA).
+#define CONV_MMA_WARPS 3
+template <bool PAIR>
+__global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES];
-    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_empty, acc_full, acc_ready;
+    __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES], w_peer[CONV_MAX_STAGES];
+    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_peer, img_empty, acc_full, acc_ready;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
     const int chunks_in = p.cin >> 3;
     const uint32_t img_bytes = (uint32_t)chunks_in * p.R_in * 16;
-    const uint32_t stage_bytes = (uint32_t)p.kp * p.nb * 2;
+    const int nb_loc = PAIR ? p.nb >> 1 : p.nb;                 // weight rows (output channels) this CTA keeps per stage
+    const uint32_t stage_bytes = (uint32_t)p.kp * nb_loc * 2;
     uint8_t *img = smem;
     uint8_t *ring = smem + ((img_bytes + 1023) & ~1023u);
     const int taps = p.ksize * p.ksize;
     const int nkp = p.cin / p.kp;
     const int nnb = p.cout / p.nb;
     const int chunks_kp = p.kp >> 3;
+    // positions: one per CTA; a pair walks two neighbouring positions together (the second may not exist when n is odd)
+    const int pos_first = PAIR ? 2 * (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int pos_step = PAIR ? (int)(gridDim.x & ~1u) : (int)gridDim.x;
 
     dg_pdl_launch_dependents();
     if (threadIdx.x == 0) {
         DBG_STAMP(0);
-        for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], CONV_MMA_WARPS); mbar_init(&w_peer[s], 1); }
         for (int k = 0; k < nkp; ++k) mbar_init(&img_full[k], 1);
-        mbar_init(&img_empty, 1);
-        mbar_init(&acc_full, 1);
-        mbar_init(&acc_ready, 8);
+        mbar_init(&img_peer, 1);
+        mbar_init(&img_empty, CONV_MMA_WARPS);    // every MMA-issuing warp commits its own MMAs
+        mbar_init(&acc_full, CONV_MMA_WARPS);
+        mbar_init(&acc_ready, PAIR ? 16 : 8);
         fence_barrier_init();
     }
-    if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
+    if (warp == 1) {
+        if (PAIR) { tmem_alloc2(&tmem_base_s, 512); tmem_relinquish2(); }
+        else { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
+    }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
     dg_pdl_wait();                 // everything above overlapped the previous kernel's tail; its output is visible from here on
@@ -106,9 +121,10 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
         uint32_t s = 0, ph = 0, j = 0;
         const uint32_t panel_bytes = (uint32_t)chunks_kp * p.R_in * 16;
         const size_t tap_stride = (size_t)chunks_in * p.cout * 16, kp_stride = (size_t)chunks_kp * p.cout * 16;
-        for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
+        for (int pb = pos_first; pb < p.n; pb += pos_step, ++j) {
+            const int pos = pb + (int)rank;
             mbar_wait(&img_empty, (j & 1) ^ 1);
-            if (elect_one()) {
+            if (pos < p.n && elect_one()) {
                 const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
                 for (int k = 0; k < nkp; ++k) {
                     mbar_arrive_expect_tx(&img_full[k], panel_bytes);
@@ -121,7 +137,7 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
             __syncwarp();
             for (int l = 0; l < p.nchain; ++l)
                 for (int nbk = 0; nbk < nnb; ++nbk) {
-                    const uint8_t *w_k = (const uint8_t *)p.w[l] + (size_t)nbk * p.nb * 16;
+                    const uint8_t *w_k = (const uint8_t *)p.w[l] + ((size_t)nbk * p.nb + (size_t)rank * nb_loc) * 16;
                     for (int k = 0; k < nkp; ++k, w_k += kp_stride) {
                         const uint8_t *wsrc = w_k;
                         for (int t = 0; t < taps; ++t, wsrc += tap_stride) {
@@ -129,12 +145,12 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
                             if (elect_one()) {
                                 mbar_arrive_expect_tx(&w_full[s], stage_bytes);
                                 uint8_t *dst = ring + (size_t)s * stage_bytes;
-                                // W[t][k*chunks_kp + c][nbk*nb .. +nb][8]
-                                if (nnb == 1) {
+                                // W[t][k*chunks_kp + c][nbk*nb (+ rank*nb/2) .. ][8]
+                                if (nnb == 1 && !PAIR) {
                                     bulk_g2s(dst, wsrc, stage_bytes, &w_full[s]);
                                 } else {
                                     for (int c = 0; c < chunks_kp; ++c)
-                                        bulk_g2s(dst + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
+                                        bulk_g2s(dst + (size_t)c * nb_loc * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)nb_loc * 16, &w_full[s]);
                                 }
                             }
                             __syncwarp();
@@ -143,90 +159,98 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
                     }
                 }
         }
-    } else if (warp == 1) {
-        // ===== MMA warp (converged, so descriptors stay in uniform registers; one elected lane issues) =====
-        const uint32_t idesc = make_idesc_bf16(128, p.nb, 0, 0);
+    } else if (warp == 1 && PAIR && rank == 1) {
+        // ===== relay warp of the second CTA: tells the leader when this CTA's image and weight halves have landed =====
+        const uint32_t r_img = mapa_u32(smem_u32(&img_peer), 0);
+        uint32_t s = 0, ph = 0, j = 0;
+        for (int pb = pos_first; pb < p.n; pb += pos_step, ++j) {
+            const bool has_pos = pb + 1 < p.n;
+            for (int l = 0; l < p.nchain; ++l) {
+                if (l == 0) {
+                    if (has_pos) for (int k = 0; k < nkp; ++k) mbar_wait(&img_full[k], j & 1);
+                    if (elect_one()) mbar_arrive_remote(r_img);
+                    __syncwarp();
+                }
+                for (int t = 0; t < taps * nkp * nnb; ++t) {
+                    mbar_wait(&w_full[s], ph);
+                    if (elect_one()) mbar_arrive_remote(mapa_u32(smem_u32(&w_peer[s]), 0));
+                    __syncwarp();
+                    if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (PAIR && rank == 1 && warp >= 10) {
+        // second CTA of a pair: the leader issues all MMAs
+    } else if (warp == 1 || warp >= 10) {
+        // ===== three MMA warps (each converged, so descriptors stay in uniform registers; one elected lane issues) =====
+        // The tensor pipe's queue is shallow (measured, tools/umma_rate.cu: a gap in the issue stream is ~90% exposed), so
+        // whatever an issuing thread does between MMAs -- barrier waits, commits, counters -- idles the pipe.  Each of the
+        // three warps owns one accumulator tile (tile % 3) and walks every weight stage for it: while one warp does its
+        // per-stage bookkeeping the other two keep the pipe fed, and every accumulator still sees its MMAs from a single
+        // thread in program order (bit-reproducible, no cross-thread hazard on a TMEM tile).
+        const int mma_id = warp == 1 ? 0 : warp - 9;
+        const uint32_t idesc = make_idesc_bf16(PAIR ? 256 : 128, p.nb, 0, 0);
         const uint32_t img_a = smem_u32(img), ring_a = smem_u32(ring);
         const uint32_t hi = desc_hi(128);
         const uint32_t a_lo_first = desc_lo(img_a, (uint32_t)p.R_in * 16) + (uint32_t)(p.first - p.pad_in * p.pitch_in - p.pad_in);
-        const uint32_t b_lo_ring = desc_lo(ring_a, (uint32_t)p.nb * 16);
-        const uint32_t a_kstep = 2u * p.R_in, b_kstep = 2u * p.nb, stage_units = stage_bytes >> 4;
+        const uint32_t b_lo_ring = desc_lo(ring_a, (uint32_t)nb_loc * 16);
+        const uint32_t a_kstep = 2u * p.R_in, b_kstep = 2u * nb_loc, stage_units = stage_bytes >> 4;
         const uint32_t a_panel = (uint32_t)chunks_kp * p.R_in;
         const int ksteps = p.kp >> 4;
         uint32_t s = 0, ph = 0, j = 0, a = 0;
         uint32_t b_lo_s = b_lo_ring;
         long long wait_cycles = 0;
-        for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x, ++j) {
+        auto wait_stage = [&](uint32_t st, uint32_t phase) {
+            mbar_wait(&w_full[st], phase);
+            if (PAIR) mbar_wait_cluster(&w_peer[st], phase);
+            tc_fence_after();
+        };
+        for (int pb = pos_first; pb < p.n; pb += pos_step, ++j) {
             for (int l = 0; l < p.nchain; ++l)
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
                     // the epilogue warps have drained the previous accumulators, written the previous layer's output rows
                     // into the shared-memory image (chains) and, in forward mode, pre-loaded the accumulators with the bias
-                    mbar_wait(&acc_ready, a & 1);
+                    if (PAIR) mbar_wait_cluster(&acc_ready, a & 1); else mbar_wait(&acc_ready, a & 1);
                     tc_fence_after();
-                    if (lane == 0 && j == 0) CHAIN_STAMP(l, 0);
+                    if (lane == 0 && j == 0 && mma_id == 0) CHAIN_STAMP(l, 0);
                     uint32_t a_lo_k = a_lo_first;
-                    uint32_t first_mma = p.mode == 0 ? 1u : 0u;       // 0 until the first MMA of this accumulator set has been issued
-                    // The barrier of stage i+1 is waited for between the two halves of stage i's MMAs, so its latency (and the
-                    // commit / elect bookkeeping) is covered by MMAs already queued on the tensor pipe instead of draining it.
-                    const int kh = ksteps >> 1;                       // first half: k-steps [0, kh), second: [kh, ksteps)
-                    bool stage_ready = false;
+                    const uint32_t first_mma = 1u;                    // accumulators are pre-loaded (bias, or zeros in backward mode)
                     for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
-                        if (l == 0 && nbk == 0) { mbar_wait(&img_full[k], j & 1); if (j == 0 && lane == 0) DBG_STAMP(2 + (k > 0)); }
+                        if (l == 0 && nbk == 0) {
+                            mbar_wait(&img_full[k], j & 1);
+                            if (PAIR && k == 0) mbar_wait_cluster(&img_peer, j & 1);
+                            if (j == 0 && lane == 0 && mma_id == 0) DBG_STAMP(2 + (k > 0));
+                        }
                         uint32_t a_lo_ky = a_lo_k;                    // + ky*pitch + kx rows, in 16-byte units
                         for (int ky = 0; ky < p.ksize; ++ky, a_lo_ky += p.pitch_in) {
                             for (int kx = 0; kx < p.ksize; ++kx) {
-                                if (!stage_ready) {
-                                    const long long tw0 = p.dbg ? clock64() : 0;
-                                    mbar_wait(&w_full[s], ph);
-                                    if (p.dbg) wait_cycles += clock64() - tw0;
-                                    tc_fence_after();
-                                }
-                                const bool last_stage = (k == nkp - 1) && (ky == p.ksize - 1) && (kx == p.ksize - 1);
-                                const uint32_t s_next = (s + 1 == (uint32_t)p.nstages) ? 0u : s + 1;
-                                const uint32_t ph_next = (s + 1 == (uint32_t)p.nstages) ? ph ^ 1u : ph;
+                                const long long tw0 = p.dbg ? clock64() : 0;
+                                wait_stage(s, ph);
+                                if (p.dbg) wait_cycles += clock64() - tw0;
                                 if (elect_one()) {
-                                    uint32_t a_tile = a_lo_ky + kx;
-                                    uint32_t d_tmem = tmem_base;
-                                    for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
-                                        uint32_t a_lo = a_tile, b_lo = b_lo_s;
+                                    for (int tile = mma_id; tile < p.ntiles; tile += CONV_MMA_WARPS) {
+                                        uint32_t a_lo = a_lo_ky + kx + (uint32_t)tile * 128, b_lo = b_lo_s;
+                                        const uint32_t d_tmem = tmem_base + (uint32_t)tile * p.nb;
 #pragma unroll 4
-                                        for (int ks = 0; ks < kh; ++ks, a_lo += a_kstep, b_lo += b_kstep)
-                                            mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma | (uint32_t)ks);
+                                        for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep) {
+                                            if (PAIR) mma_bf16_pair(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma);
+                                            else mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma);
+                                        }
                                     }
+                                    if (PAIR) mma_commit_pair(&w_empty[s], 3); else mma_commit(&w_empty[s]);
                                 }
                                 __syncwarp();
-                                if (!last_stage) {                    // next stage's weights: wait while this stage's MMAs execute
-                                    mbar_wait(&w_full[s_next], ph_next);
-                                    tc_fence_after();
-                                    stage_ready = true;
-                                } else {
-                                    stage_ready = false;
-                                }
-                                if (elect_one()) {
-                                    uint32_t a_tile = a_lo_ky + kx + (uint32_t)kh * a_kstep;
-                                    uint32_t d_tmem = tmem_base;
-                                    for (int tile = 0; tile < p.ntiles; ++tile, a_tile += 128, d_tmem += p.nb) {
-                                        uint32_t a_lo = a_tile, b_lo = b_lo_s + (uint32_t)kh * b_kstep;
-#pragma unroll 4
-                                        for (int ks = kh; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep)
-                                            mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, 1u);
-                                    }
-                                    mma_commit(&w_empty[s]);
-                                }
-                                __syncwarp();
-                                first_mma = 1;
                                 b_lo_s += stage_units;
-                                s = s_next; ph = ph_next;
-                                if (s == 0) b_lo_s = b_lo_ring;
+                                if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; b_lo_s = b_lo_ring; }
                             }
                         }
                     }
-                    if (elect_one()) mma_commit(&acc_full);
+                    if (elect_one()) { if (PAIR) mma_commit_pair(&acc_full, 3); else mma_commit(&acc_full); }
                     __syncwarp();
-                    if (lane == 0 && j == 0) CHAIN_STAMP(l, 1);
-                    if (a == 0 && lane == 0) { DBG_STAMP(4); if (p.dbg) p.dbg[blockIdx.x * 8 + 7] = wait_cycles; }
+                    if (lane == 0 && j == 0 && mma_id == 0) CHAIN_STAMP(l, 1);
+                    if (a == 0 && lane == 0 && mma_id == 0) { DBG_STAMP(4); if (p.dbg) p.dbg[blockIdx.x * 8 + 7] = wait_cycles; }
                 }
-            if (elect_one()) mma_commit(&img_empty);
+            if (elect_one()) { if (PAIR) mma_commit_pair(&img_empty, 3); else mma_commit(&img_empty); }
             __syncwarp();
         }
     } else {
@@ -237,13 +261,14 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
         const int nblk32 = p.nb >> 5;
         const int my_blocks = (nblk32 - half + 1) >> 1;           // blocks half, half+2, ...
         const int items = p.ntiles * my_blocks;
+        bool has_pos_flag = true;                                  // false: this CTA of a pair has no position (n odd); nothing is loaded or stored
         auto row_of = [&](int item, int l, int &rho, int &rho_out, int &rho_m, bool &valid, int &tile, int &c0) {
             tile = item / my_blocks;
             c0 = ((item - tile * my_blocks) * 2 + half) * 32;
             rho = p.first + tile * 128 + q * 32 + lane;
             const int xp = rho / p.pitch_in, yp = rho - xp * p.pitch_in;
             const int x = xp - p.pad_in, y = yp - p.pad_in;
-            valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+            valid = has_pos_flag && x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
             // intermediate layers of a chain keep the input geometry; only the last layer's HBM output may differ
             rho_out = l == p.nchain - 1 ? (x + p.pad_out) * p.pitch_out + y + p.pad_out : rho;
             rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
@@ -258,47 +283,60 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
                 uint32_t r[32];
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-                    if (valid) {
-                        const float4 *bp = reinterpret_cast<const float4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8);
-                        b0 = __ldg(bp); b1 = __ldg(bp + 1);
-                    }
-                    r[g * 8 + 0] = __float_as_uint(b0.x); r[g * 8 + 1] = __float_as_uint(b0.y);
-                    r[g * 8 + 2] = __float_as_uint(b0.z); r[g * 8 + 3] = __float_as_uint(b0.w);
-                    r[g * 8 + 4] = __float_as_uint(b1.x); r[g * 8 + 5] = __float_as_uint(b1.y);
-                    r[g * 8 + 6] = __float_as_uint(b1.z); r[g * 8 + 7] = __float_as_uint(b1.w);
+                    uint4 bw = make_uint4(0u, 0u, 0u, 0u);
+                    if (valid) bw = __ldg(reinterpret_cast<const uint4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8));
+                    r[g * 8 + 0] = bw.x << 16; r[g * 8 + 1] = bw.x & 0xFFFF0000u;        // bf16 -> fp32 bit patterns
+                    r[g * 8 + 2] = bw.y << 16; r[g * 8 + 3] = bw.y & 0xFFFF0000u;
+                    r[g * 8 + 4] = bw.z << 16; r[g * 8 + 5] = bw.z & 0xFFFF0000u;
+                    r[g * 8 + 6] = bw.w << 16; r[g * 8 + 7] = bw.w & 0xFFFF0000u;
                 }
                 tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
             }
             tmem_st_wait();
         };
+        // backward mode: the accumulators start at zero (every MMA accumulates; two warps issue, no MMA is "the first")
+        auto preload_zero = [&]() {
+            uint32_t r[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) r[e] = 0u;
+            for (int item = 0; item < items; ++item) {
+                const int tile = item / my_blocks, c0 = ((item - tile * my_blocks) * 2 + half) * 32;
+                tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+            }
+            tmem_st_wait();
+        };
         // one item's bias (32 channels of one row) of layer l into registers
-        auto load_bias_item = [&](int item, int l, float4 (&bq)[8]) {
+        auto load_bias_item = [&](int item, int l, uint4 (&bq)[4]) {
             int rho, rho_out, rho_m, tile, c0; bool valid;
             row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
             const int R_b = l == p.nchain - 1 ? p.R_out : p.R_in;
             const int chunk0 = c0 >> 3;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-                bq[2 * g] = make_float4(0.f, 0.f, 0.f, 0.f); bq[2 * g + 1] = bq[2 * g];
-                if (valid) {
-                    const float4 *bp = reinterpret_cast<const float4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8);
-                    bq[2 * g] = __ldg(bp); bq[2 * g + 1] = __ldg(bp + 1);
-                }
+                bq[g] = make_uint4(0u, 0u, 0u, 0u);
+                if (valid) bq[g] = __ldg(reinterpret_cast<const uint4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8));
             }
         };
+        // hand-over to the MMA warp: in a pair the barrier lives in the leader CTA (the second CTA arrives remotely)
+        const uint32_t r_acc_ready = PAIR ? mapa_u32(smem_u32(&acc_ready), 0) : 0u;
+        auto arrive_ready = [&]() {
+            if (lane == 0) { if (PAIR && rank == 1) mbar_arrive_remote(r_acc_ready); else mbar_arrive(&acc_ready); }
+        };
         uint32_t a = 0;
-        for (int pos = blockIdx.x; pos < p.n; pos += gridDim.x) {
+        for (int pb = pos_first; pb < p.n; pb += pos_step) {
+            const int pos = pb + (int)rank;
+            const bool has_pos = pos < p.n;                        // the second CTA of the last pair may have no position
+            has_pos_flag = has_pos;
             for (int l = 0; l < p.nchain; ++l)
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
                     const bool chain_more = l + 1 < p.nchain;      // this layer's output is the next layer's shared-memory image
                     if (l == 0 || nnb > 1) {
-                        // first layer of a position (or a multi-N-block layer): hand the accumulators to the MMA warp here;
+                        // first layer of a position (or a multi-N-block layer): hand the accumulators to the MMA warps here;
                         // inside a chain the hand-over happens at the end of the previous layer's drain
-                        if (p.mode == 0) preload_bias(l, nbk);
+                        if (p.mode == 0) preload_bias(l, nbk); else preload_zero();
                         tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&acc_ready);
+                        arrive_ready();
                     }
                     // backward: the ReLU mask of each item is compressed to one 32-bit word while the MMAs run
                     uint32_t masks[8];
@@ -331,12 +369,12 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
                     // inside a forward chain the next layer's bias is fetched one item ahead of the drain (the first item while
                     // the MMAs still run) and written into each accumulator block right after that block has been drained
                     const bool bias_pipe = chain_more && p.mode == 0;
-                    float4 bq[2][8];
-                    if (bias_pipe) load_bias_item(0, l + 1, bq[0]);
+                    uint4 bq[3][4];                                // bf16 bias of three items in flight: two ahead of the drain
+                    if (bias_pipe) { load_bias_item(0, l + 1, bq[0]); if (items > 1) load_bias_item(1, l + 1, bq[1]); }
                     mbar_wait(&acc_full, a & 1);
                     tc_fence_after();
                     if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
-                    if (threadIdx.x == 64 && pos == (int)blockIdx.x) CHAIN_STAMP(l, 2);
+                    if (threadIdx.x == 64 && pb == pos_first) CHAIN_STAMP(l, 2);
                     const int R_o = chain_more ? p.R_in : p.R_out;
 #pragma unroll
                     for (int item = 0; item < 8; ++item) {
@@ -346,7 +384,7 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
                         const int chunk0 = (nbk * p.nb + c0) >> 3;
                         uint32_t r[32];
                         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
-                        if (bias_pipe && item + 1 < items) load_bias_item(item + 1, l + 1, bq[(item + 1) & 1]);
+                        if (bias_pipe && item + 2 < items) load_bias_item(item + 2, l + 1, bq[(item + 2) % 3]);
                         tmem_ld_wait();
                         if (valid) {
                             const uint32_t mbits = masks[item];
@@ -368,35 +406,42 @@ __global__ void __launch_bounds__(320, 1) conv_umma_kernel(const __grid_constant
                                 if (chain_more) *reinterpret_cast<uint4 *>(img + ((size_t)(chunk0 + g) * p.R_in + rho) * 16) = o;
                             }
                         }
-                        if (bias_pipe) {
-                            const float4 (&bb)[8] = bq[item & 1];
+                        if (chain_more && p.mode != 0) {
 #pragma unroll
-                            for (int g = 0; g < 8; ++g) {
-                                r[g * 4 + 0] = __float_as_uint(bb[g].x); r[g * 4 + 1] = __float_as_uint(bb[g].y);
-                                r[g * 4 + 2] = __float_as_uint(bb[g].z); r[g * 4 + 3] = __float_as_uint(bb[g].w);
+                            for (int e = 0; e < 32; ++e) r[e] = 0u;
+                            tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+                        }
+                        if (bias_pipe) {
+                            const uint4 (&bb)[4] = bq[item % 3];
+#pragma unroll
+                            for (int g = 0; g < 4; ++g) {
+                                r[g * 8 + 0] = bb[g].x << 16; r[g * 8 + 1] = bb[g].x & 0xFFFF0000u;
+                                r[g * 8 + 2] = bb[g].y << 16; r[g * 8 + 3] = bb[g].y & 0xFFFF0000u;
+                                r[g * 8 + 4] = bb[g].z << 16; r[g * 8 + 5] = bb[g].z & 0xFFFF0000u;
+                                r[g * 8 + 6] = bb[g].w << 16; r[g * 8 + 7] = bb[g].w & 0xFFFF0000u;
                             }
                             tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
                         }
                     }
                     if (chain_more) {
                         // next layer: its accumulators (bias) and its input image are ready once every epilogue warp gets here
-                        if (bias_pipe) tmem_st_wait();
+                        tmem_st_wait();
                         fence_proxy_async();                       // generic-proxy st.shared -> visible to the tensor core's async proxy
                         tc_fence_before();
                         __syncwarp();
-                        if (lane == 0) mbar_arrive(&acc_ready);
+                        arrive_ready();
                     } else {
                         tc_fence_before();
                         __syncwarp();
                     }
                     if (a == 0 && threadIdx.x == 64) DBG_STAMP(6);
-                    if (threadIdx.x == 64 && pos == (int)blockIdx.x) CHAIN_STAMP(l, 3);
+                    if (threadIdx.x == 64 && pb == pos_first) CHAIN_STAMP(l, 3);
                 }
         }
     }
     tc_fence_before();
-    __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, 512);
+    if (PAIR) cluster_sync_all(); else __syncthreads();          // a pair: neither CTA may leave while the other still uses its memory
+    if (warp == 1) { if (PAIR) tmem_dealloc2(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
     if (threadIdx.x == 0 && p.dbg) p.dbg[148 * 8 + blockIdx.x * 2 + 1] = dg_globaltimer();
 }
 
@@ -1010,11 +1055,11 @@ __global__ void __launch_bounds__(384) planes_to_blocked_kernel(const float *__r
 // master fp32 (Torch7 order) -> bf16 MMA operands of one layer:
 //   wf[t][ci/8][co][8]  = W[co][ci][t]            (forward B operand; ci >= cin_true -> 0)
 //   wd[t][co/8][ci][8]  = W[co][ci][KK-1-t]       (input-gradient B operand, taps flipped); may be NULL
-//   ab[c/8][rho][8]     = b[c] + a[c][x][y]       (fp32 epilogue bias in the OUTPUT geometry)
+//   ab[c/8][rho][8]     = bf16(b[c] + a[c][x][y]) (epilogue bias in the OUTPUT geometry)
 struct PackLayer {
     const float *W, *b, *a;
     bf16 *wf, *wd;
-    float *ab;
+    bf16 *ab;
     int cin_true, cin, cout, ksize;
 };
 
@@ -1024,7 +1069,7 @@ __global__ void __launch_bounds__(256) pack_layer_kernel(const PackLayer *__rest
     const PackLayer pl = table[blockIdx.y];
     const float *__restrict__ W = pl.W, *__restrict__ b = pl.b, *__restrict__ a = pl.a;
     bf16 *__restrict__ wf = pl.wf, *__restrict__ wd = pl.wd;
-    float *__restrict__ ab = pl.ab;
+    bf16 *__restrict__ ab = pl.ab;
     const int cin_true = pl.cin_true, cin = pl.cin, cout = pl.cout, ksize = pl.ksize;
     const int KK = ksize * ksize;
     const int nwf = KK * cin * cout;
@@ -1046,7 +1091,7 @@ __global__ void __launch_bounds__(256) pack_layer_kernel(const PackLayer *__rest
         const int c = idx / DG_POINTS, pt = idx - c * DG_POINTS;
         const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
         const int rho = (x + pad_out) * pitch_out + y + pad_out;
-        ab[((size_t)(c >> 3) * R_out + rho) * 8 + (c & 7)] = b[c] + a[idx];
+        ab[((size_t)(c >> 3) * R_out + rho) * 8 + (c & 7)] = __float2bfloat16(b[c] + a[idx]);
     }
 }
 
@@ -1058,7 +1103,7 @@ struct SgdPackLayer {
     float *W, *b, *a;            // master parameters of the layer (Torch7 order)
     const float *gW, *gb, *ga;   // gradients
     bf16 *wf, *wd;
-    float *ab;
+    bf16 *ab;
     int cin_true, cin, cout, ksize;
 };
 
@@ -1102,7 +1147,7 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
         if (L.ab) {
             const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
             const int rho = (x + pad_out) * pitch_out + y + pad_out;
-            L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + r] = v + bnew[r];
+            L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + r] = __float2bfloat16(v + bnew[r]);
         }
     }
     if (!L.wf) return;
@@ -1136,7 +1181,7 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
 // ---------------------------------------------------------------------------------------------
 struct LayerOps {
     bf16 *wf = nullptr, *wd = nullptr;
-    float *ab = nullptr;
+    bf16 *ab = nullptr;
     int cin_pad = 0;
 };
 
@@ -1186,16 +1231,23 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     if (timeline && !dbg) cudaMalloc(&dbg, (148 * 10 + 64) * sizeof(long long));
     cp.dbg = timeline ? dbg : nullptr;
     const size_t img_bytes = ((size_t)(cp.cin / 8) * cp.R_in * 16 + 1023) & ~(size_t)1023;
-    const size_t stage = (size_t)cp.kp * cp.nb * 2;
+    // CTA pairs (cta_group::2) when the layer is one N block and one K panel: each CTA keeps half of every weight stage
+    // (opt-in, DG_PAIR=1: measured slower at batch 128 -- the two SMs of a TPC then drain their accumulators in lock-step and
+    // contend for the TPC's path to L2, which costs more than the MMA phase gains)
+    static const bool want_pair = getenv("DG_PAIR") != nullptr;
+    const bool pair = want_pair && cp.cout == cp.nb && cp.cin == cp.kp && cp.nb % 32 == 0 && cp.n >= 2;
+    const size_t stage = (size_t)cp.kp * (pair ? cp.nb / 2 : cp.nb) * 2;
     const size_t budget = 227 * 1024 - 1024;       // static smem (barriers) lives in the remaining KB
     DG_REQUIRE(img_bytes + 2 * stage <= budget, "bf16 path: image (%zu B) + weight ring do not fit shared memory", img_bytes);
     int ns = (int)((budget - img_bytes) / stage);
     if (ns > CONV_MAX_STAGES) ns = CONV_MAX_STAGES;
     cp.nstages = ns;
     const size_t smem = img_bytes + ns * stage;
-    const int grid = cp.n < m->bf->num_sms ? cp.n : m->bf->num_sms;
+    int grid = cp.n < m->bf->num_sms ? cp.n : m->bf->num_sms;
+    if (pair) grid = 2 * std::min((cp.n + 1) / 2, m->bf->num_sms / 2);
     { dg_prof_scope _ps(c, cp.mode ? DG_K_DGRAD : (cp.ksize == 5 || cp.cin < cp.cout ? DG_K_CONV_FIRST : DG_K_CONV));
-    DG_CUDA(dg_launch_pdl(conv_umma_kernel, dim3(grid), dim3(320), smem, c->stream, cp));
+    if (pair) DG_CUDA(dg_launch_pdl(conv_umma_kernel<true>, dim3(grid), dim3(384), smem, c->stream, cp, 2));
+    else DG_CUDA(dg_launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(384), smem, c->stream, cp));
     }
     c->launches++;
     if (timeline) {
@@ -1284,7 +1336,7 @@ int dg_bf16_create(dg_model *m) {
         const size_t nw = (size_t)li.k * li.k * o.cin_pad * li.cout;
         if (int rc = alloc0((void **)&o.wf, nw * 2)) return rc;
         if (l > 0) if (int rc = alloc0((void **)&o.wd, nw * 2)) return rc;
-        if (int rc = alloc0((void **)&o.ab, (size_t)li.cout * DG_R3 * 4)) return rc;
+        if (int rc = alloc0((void **)&o.ab, (size_t)li.cout * DG_R3 * 2)) return rc;
         WgradPlan w;
         if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, l == 0 ? b->g_first : b->g3, w)) return rc;
         if (w.scratch_bytes > scratch) scratch = w.scratch_bytes;
@@ -1335,7 +1387,8 @@ int dg_bf16_create(dg_model *m) {
     DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
     cudaEvent_t *evs[] = {&b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
     for (cudaEvent_t *e : evs) DG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
-    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
     DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
     DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
     return 0;

@@ -79,7 +79,10 @@ def forward(flat, x, num_layers, channel_size, quant=None):
     for i, (W, b, a) in enumerate(layers):
         k = W.shape[-1]
         Wq = _q(W, quant) if i < len(layers) - 1 else W         # the 1-channel head keeps fp32 weights on the GPU
-        z = F.conv2d(h, Wq, None, padding=(k - 1) // 2) + b.view(1, -1, 1, 1) + a.unsqueeze(0)
+        bias = b.view(-1, 1, 1) + a                               # per-channel + per-point bias (experiments.lua:138,143-145)
+        if i < len(layers) - 1:
+            bias = _q(bias, quant)                                # the GPU's bf16 epilogue operand; the head keeps fp32
+        z = F.conv2d(h, Wq, None, padding=(k - 1) // 2) + bias.unsqueeze(0)
         zs.append(z)
         h = torch.relu(z)
         if i < len(layers) - 1:

@@ -5,15 +5,16 @@
 #include <cstdio>
 #include <vector>
 using namespace umma;
+__device__ __forceinline__ uint32_t b_lo_dummy(uint32_t x) { return x; }
 
-struct RCfg { int N, nmma, nacc, a_mn, b_mn, layout, a_lbo, a_sbo, b_lbo, b_sbo, a_stride, b_stride, a_span, b_span, a_off; };
+struct RCfg { int N, nmma, nacc, a_mn, b_mn, layout, a_lbo, a_sbo, b_lbo, b_sbo, a_stride, b_stride, a_span, b_span, a_off, group, gap; };
 
 __global__ void __launch_bounds__(128) rate_kernel(RCfg c, long long *out) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ uint64_t bar;
+    __shared__ uint64_t bar, bar2;
     __shared__ uint32_t tmem_base;
     for (int i = threadIdx.x; i < 200 * 1024 / 4; i += blockDim.x) ((uint32_t *)smem)[i] = 0x3c003c00u;
-    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&bar2, 1 << 20); fence_barrier_init(); }
     if (threadIdx.x < 32) { tmem_alloc(&tmem_base, 512); tmem_relinquish(); }
     fence_proxy_async();
     tc_fence_before();
@@ -32,7 +33,13 @@ __global__ void __launch_bounds__(128) rate_kernel(RCfg c, long long *out) {
             for (int i = 0; i < c.nmma; i += 8) {
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
-                    mma_bf16(tmem_base + (j % c.nacc) * c.N, desc_join(alo[j], hi_a), desc_join(blo[j], hi_b), idesc, (i | (j >= c.nacc)) != 0);
+                    mma_bf16(tmem_base + (j % c.nacc) * c.N, desc_join(alo[j], hi_a), desc_join(b_lo_dummy(blo[j]), hi_b), idesc, (i | (j >= c.nacc)) != 0);
+                if (c.group && ((i + 8) % c.group) == 0 && i + 8 < c.nmma) {
+                    // stage boundary as in the conv kernel: commit to a barrier nobody waits on, then `gap` cycles of scalar work
+                    mma_commit(&bar2);
+                    const long long g0 = clock64();
+                    while (clock64() - g0 < c.gap) { }
+                }
             }
             mma_commit(&bar);
         }
@@ -86,6 +93,13 @@ int main() {
         s = RCfg{128, 512, 1, 0, 0, 2, 16, 1024, 16, 1024, 32, 32, 4, 4, 128}; run("K-major SW128 N=128, A start +1 row (128 B)", s, grid);
         s.a_off = 21 * 128; run("K-major SW128 N=128, A start +21 rows", s, grid);
         s = RCfg{128, 512, 1, 1, 1, 2, 8192, 1024, 8192, 1024, 2048, 2048, 4, 4, 128}; run("MN-major SW128 N=128, A start +1 row", s, grid);
+        // stage boundaries: a commit every `group` MMAs, followed by `gap` cycles in which the issuing thread does something else
+        for (int gap : {0, 100, 200, 400, 800}) {
+            RCfg g = k128; g.nmma = 480; g.nacc = 3; g.group = 24; g.gap = gap;
+            char nm[96]; snprintf(nm, sizeof nm, "K-major N=128: commit every 24 MMAs + %d-cycle gap", gap);
+            run(nm, g, grid);
+        }
+        { RCfg g = k128; g.nmma = 480; g.nacc = 3; g.group = 8; g.gap = 0; run("K-major N=128: commit every 8 MMAs, no gap", g, grid); }
     }
     return 0;
 }
