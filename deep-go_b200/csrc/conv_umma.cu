@@ -469,7 +469,7 @@ struct WgradParams {
 
 #define WG_RP 128         // K rows per stage
 
-__global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
+__global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full, acc_empty;
     __shared__ uint32_t tmem_base_s;
@@ -492,8 +492,8 @@ __global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constan
     dg_pdl_launch_dependents();
     if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8] = clock64();
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], 1); }
-        mbar_init(&acc_full, 1);
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], CONV_MMA_WARPS); }
+        mbar_init(&acc_full, CONV_MMA_WARPS);     // three MMA-issuing warps, one kernel column (kx accumulator) each
         mbar_init(&acc_empty, 8);
         fence_barrier_init();
     }
@@ -531,7 +531,10 @@ __global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constan
                 if (panel >= panels) { panel -= panels; ++pos; }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp >= 10) {
+        // three MMA warps: warp i issues the MMAs of kernel columns kx = i, i+3, .. (disjoint accumulators), so the shallow
+        // tensor-pipe queue always has work while another warp waits on a panel barrier or commits (see conv_umma_kernel)
+        const int mma_id = warp == 1 ? 0 : warp - 9;
         const uint32_t idesc = make_idesc_bf16(128, p.nb, 1, 1);
         const uint32_t hi_a = desc_hi(WG_RP * 16), hi_b = desc_hi((uint32_t)rb_pad * 16);
         const uint32_t a_lo_ring = desc_lo(smem_u32(smem), 128), b_lo_ring = desc_lo(smem_u32(smem) + a_bytes, 128);
@@ -539,7 +542,7 @@ __global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constan
         uint32_t s = 0, ph = 0;
         uint32_t a_lo_s = a_lo_ring, b_lo_s = b_lo_ring;
         long long wcy = 0;
-        if (lane == 0 && p.dbg) p.dbg[blockIdx.x * 8 + 1] = clock64();
+        if (lane == 0 && p.dbg && mma_id == 0) p.dbg[blockIdx.x * 8 + 1] = clock64();
         for (int li = 0; li < p.nl; ++li) {
             mbar_wait(&acc_empty, (li & 1) ^ 1);              // the drain warps have read the previous layer's accumulators
             tc_fence_after();
@@ -550,8 +553,8 @@ __global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constan
                 if (p.dbg) wcy += clock64() - tw0;
                 tc_fence_after();
                 if (elect_one()) {
-                    uint32_t d_tmem = tmem_base;
-                    for (int kx = 0; kx < p.ksize; ++kx, d_tmem += p.nb) {
+                    for (int kx = mma_id; kx < p.ksize; kx += CONV_MMA_WARPS) {
+                        const uint32_t d_tmem = tmem_base + (uint32_t)kx * p.nb;
                         uint32_t a_lo = a_lo_s, b_lo = b_lo_s + kx;
 #pragma unroll
                         for (int ks = 0; ks < WG_RP / 16; ++ks, a_lo += 16, b_lo += 16)
@@ -567,7 +570,7 @@ __global__ void __launch_bounds__(320, 1) wgrad_umma_kernel(const __grid_constan
             if (elect_one()) mma_commit(&acc_full);
             __syncwarp();
         }
-        if (lane == 0 && p.dbg) { p.dbg[blockIdx.x * 8 + 2] = clock64(); p.dbg[blockIdx.x * 8 + 3] = wcy; }
+        if (lane == 0 && p.dbg && mma_id == 0) { p.dbg[blockIdx.x * 8 + 2] = clock64(); p.dbg[blockIdx.x * 8 + 3] = wcy; }
     } else {
         // ===== drain warps 2..9: two warps per TMEM lane quarter, alternating 32-column blocks =====
         const int q = warp & 3, half = (warp - 2) >> 2;
@@ -1617,7 +1620,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         // deterministic path: this scratch half was last read by the reduction two layers ago
         if (b->deterministic && rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
         { dg_prof_scope _ps(c, DG_K_WGRAD);
-        DG_CUDA(dg_launch_pdl(wgrad_umma_kernel, dim3(w.combos * w.splits), dim3(320), w.smem, c->stream, wp));
+        DG_CUDA(dg_launch_pdl(wgrad_umma_kernel, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp));
         }
         c->launches++;
         if (wp.dbg) {
