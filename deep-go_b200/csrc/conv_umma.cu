@@ -471,7 +471,9 @@ struct WgradParams {
 
 __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full, acc_empty;
+    // accumulator hand-over is per MMA warp (= per group of kernel columns): the drain of warp w's columns overlaps the other
+    // warps' MMAs of the next layer
+    __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full[CONV_MMA_WARPS], acc_empty[CONV_MMA_WARPS];
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -493,8 +495,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8] = clock64();
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], CONV_MMA_WARPS); }
-        mbar_init(&acc_full, CONV_MMA_WARPS);     // three MMA-issuing warps, one kernel column (kx accumulator) each
-        mbar_init(&acc_empty, 8);
+        for (int w = 0; w < CONV_MMA_WARPS; ++w) { mbar_init(&acc_full[w], 1); mbar_init(&acc_empty[w], 8); }
         fence_barrier_init();
     }
     if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
@@ -544,7 +545,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         long long wcy = 0;
         if (lane == 0 && p.dbg && mma_id == 0) p.dbg[blockIdx.x * 8 + 1] = clock64();
         for (int li = 0; li < p.nl; ++li) {
-            mbar_wait(&acc_empty, (li & 1) ^ 1);              // the drain warps have read the previous layer's accumulators
+            mbar_wait(&acc_empty[mma_id], (li & 1) ^ 1);      // the drain warps have read this warp's accumulators of the previous layer
             tc_fence_after();
             uint32_t acc = 0;
             for (int u = split; u < units; u += p.splits) {
@@ -567,7 +568,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                 a_lo_s += stage_units; b_lo_s += stage_units;
                 if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; a_lo_s = a_lo_ring; b_lo_s = b_lo_ring; }
             }
-            if (elect_one()) mma_commit(&acc_full);
+            if (elect_one()) mma_commit(&acc_full[mma_id]);
             __syncwarp();
         }
         if (lane == 0 && p.dbg && mma_id == 0) { p.dbg[blockIdx.x * 8 + 2] = clock64(); p.dbg[blockIdx.x * 8 + 3] = wcy; }
@@ -578,12 +579,13 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         const int co = mblk * 128 + q * 32 + lane;
         const int cin4 = p.cin >> 2;
         for (int li = 0; li < p.nl; ++li) {
-            mbar_wait(&acc_full, li & 1);
-            tc_fence_after();
             float4 *gl = reinterpret_cast<float4 *>(p.gacc[li]);
             // scratch tile layout [kx][ci/4][co][4]: lane = co, so one warp-wide 16-byte access covers 512 contiguous bytes
             float4 *sc = reinterpret_cast<float4 *>(p.scratch) + ((size_t)combo * p.splits + split) * p.ksize * 32 * p.nb + (q * 32 + lane);
-            for (int kx = 0; kx < p.ksize; ++kx)
+            for (int w = 0; w < CONV_MMA_WARPS; ++w) {
+            mbar_wait(&acc_full[w], li & 1);
+            tc_fence_after();
+            for (int kx = w; kx < p.ksize; kx += CONV_MMA_WARPS)
                 for (int c0 = half * 32; c0 < p.nb; c0 += 64) {
                     uint32_t r[32];
                     const int ncol = min(32, p.nb - c0);          // nb is a multiple of 16
@@ -613,7 +615,8 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                 }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty);
+            if (lane == 0) mbar_arrive(&acc_empty[w]);
+            }
         }
     }
     tc_fence_before();
