@@ -75,6 +75,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
     __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES], w_peer[CONV_MAX_STAGES];
     __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_peer, img_empty, acc_full, acc_ready;
     __shared__ uint32_t tmem_base_s;
+    __shared__ uint32_t row_s[4][256], mask_s[8][256];          // per-thread tables of the epilogue warps (see there)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
@@ -256,66 +257,85 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
     } else {
         // ===== epilogue warps 2..9: TMEM -> registers -> ReLU or mask -> bf16 -> HBM (+ shared-memory image in a chain) =====
         // warp w may only touch TMEM lanes 32*(w%4)..+31; two warps share a lane quarter and split the 32-column blocks.
+        // An "item" is one 32-column block of one accumulator tile.  The item loops are ROLLED on purpose: fully unrolled, this
+        // branch was ~100 KB of SASS and every layer streamed it through the instruction caches (the drain ran at a quarter
+        // of the speed it has now).  What varies per item and cannot be recomputed cheaply lives in two small per-thread
+        // tables in shared memory.
         const int q = warp & 3, half = (warp - 2) >> 2;
+        const int et = (int)threadIdx.x - 64;                      // 0..255: this thread's column in the per-thread tables
         const int chunks_out = p.cout >> 3;
         const int nblk32 = p.nb >> 5;
         const int my_blocks = (nblk32 - half + 1) >> 1;           // blocks half, half+2, ...
-        const int items = p.ntiles * my_blocks;
-        bool has_pos_flag = true;                                  // false: this CTA of a pair has no position (n odd); nothing is loaded or stored
-        auto row_of = [&](int item, int l, int &rho, int &rho_out, int &rho_m, bool &valid, int &tile, int &c0) {
-            tile = item / my_blocks;
-            c0 = ((item - tile * my_blocks) * 2 + half) * 32;
-            rho = p.first + tile * 128 + q * 32 + lane;
+        const int items = p.ntiles * my_blocks;                    // <= 8 (ntiles * nb <= 512 TMEM columns)
+        const int rho0 = p.first + q * 32 + lane;                  // this thread's image row in tile 0 (+128 per tile)
+        const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+        // rows are the same for every layer and position: bit 31 = a board point, bits 12..23 = row in the geometry of the
+        // launch's last output, bits 0..11 = row in the mask geometry
+        for (int tile = 0; tile < p.ntiles; ++tile) {
+            const int rho = rho0 + tile * 128;
             const int xp = rho / p.pitch_in, yp = rho - xp * p.pitch_in;
             const int x = xp - p.pad_in, y = yp - p.pad_in;
-            valid = has_pos_flag && x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+            const bool on_board = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+            const uint32_t r_last = (uint32_t)((x + p.pad_out) * p.pitch_out + y + p.pad_out);
+            const uint32_t r_mask = (uint32_t)((x + p.pad_mask) * p.pitch_mask + y + p.pad_mask);
+            row_s[tile][et] = on_board ? (0x80000000u | (r_last << 12) | r_mask) : 0u;
+        }
+        bool has_pos_flag = true;                                  // false: this CTA of a pair has no position (n odd); nothing is loaded or stored
+        auto advance = [&](int &tile, int &blk) { if (++blk == my_blocks) { blk = 0; ++tile; } };
+        auto row_of = [&](int tile, int blk, int l, int &rho, int &rho_out, int &rho_m, bool &valid, int &c0) {
+            const uint32_t ri = row_s[tile][et];
+            c0 = (blk * 2 + half) * 32;
+            rho = rho0 + tile * 128;
+            valid = has_pos_flag && (ri >> 31);
             // intermediate layers of a chain keep the input geometry; only the last layer's HBM output may differ
-            rho_out = l == p.nchain - 1 ? (x + p.pad_out) * p.pitch_out + y + p.pad_out : rho;
-            rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
+            rho_out = l == p.nchain - 1 ? (int)((ri >> 12) & 0xFFFu) : rho;
+            rho_m = (int)(ri & 0xFFFu);
         };
-        // forward: accumulators start as bias[c] + a[c][x][y] (tcgen05.st), so the drain below has no global load
-        auto preload_bias = [&](int l, int nbk) {
-            for (int item = 0; item < items; ++item) {
-                int rho, rho_out, rho_m, tile, c0; bool valid;
-                row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
-                const int R_b = l == p.nchain - 1 ? p.R_out : p.R_in;
-                const int chunk0 = (nbk * p.nb + c0) >> 3;
-                uint32_t r[32];
+        auto bias_to_f32 = [&](const uint4 (&bq)[4], uint32_t (&r)[32]) {
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    uint4 bw = make_uint4(0u, 0u, 0u, 0u);
-                    if (valid) bw = __ldg(reinterpret_cast<const uint4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8));
-                    r[g * 8 + 0] = bw.x << 16; r[g * 8 + 1] = bw.x & 0xFFFF0000u;        // bf16 -> fp32 bit patterns
-                    r[g * 8 + 2] = bw.y << 16; r[g * 8 + 3] = bw.y & 0xFFFF0000u;
-                    r[g * 8 + 4] = bw.z << 16; r[g * 8 + 5] = bw.z & 0xFFFF0000u;
-                    r[g * 8 + 6] = bw.w << 16; r[g * 8 + 7] = bw.w & 0xFFFF0000u;
-                }
-                tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
+            for (int g = 0; g < 4; ++g) {
+                r[g * 8 + 0] = bq[g].x << 16; r[g * 8 + 1] = bq[g].x & 0xFFFF0000u;        // bf16 -> fp32 bit patterns
+                r[g * 8 + 2] = bq[g].y << 16; r[g * 8 + 3] = bq[g].y & 0xFFFF0000u;
+                r[g * 8 + 4] = bq[g].z << 16; r[g * 8 + 5] = bq[g].z & 0xFFFF0000u;
+                r[g * 8 + 6] = bq[g].w << 16; r[g * 8 + 7] = bq[g].w & 0xFFFF0000u;
             }
-            tmem_st_wait();
         };
-        // backward mode: the accumulators start at zero (every MMA accumulates; two warps issue, no MMA is "the first")
-        auto preload_zero = [&]() {
-            uint32_t r[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) r[e] = 0u;
-            for (int item = 0; item < items; ++item) {
-                const int tile = item / my_blocks, c0 = ((item - tile * my_blocks) * 2 + half) * 32;
-                tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
-            }
-            tmem_st_wait();
-        };
-        // one item's bias (32 channels of one row) of layer l into registers
-        auto load_bias_item = [&](int item, int l, uint4 (&bq)[4]) {
-            int rho, rho_out, rho_m, tile, c0; bool valid;
-            row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
+        // one item's bias (32 channels of one row) of layer l, N block nbk, into registers
+        auto load_bias_item = [&](int tile, int blk, int l, int nbk, uint4 (&bq)[4]) {
+            int rho, rho_out, rho_m, c0; bool valid;
+            row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
             const int R_b = l == p.nchain - 1 ? p.R_out : p.R_in;
-            const int chunk0 = c0 >> 3;
+            const int chunk0 = (nbk * p.nb + c0) >> 3;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
                 bq[g] = make_uint4(0u, 0u, 0u, 0u);
                 if (valid) bq[g] = __ldg(reinterpret_cast<const uint4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8));
             }
+        };
+        // forward: accumulators start as bias[c] + a[c][x][y] (tcgen05.st), so the drain below has no global load
+        auto preload_bias = [&](int l, int nbk) {
+            int tile = 0, blk = 0;
+            for (int item = 0; item < items; ++item) {
+                uint4 bq[4];
+                uint32_t r[32];
+                load_bias_item(tile, blk, l, nbk, bq);
+                bias_to_f32(bq, r);
+                tmem_st32(tm_lane + tile * p.nb + (blk * 2 + half) * 32, r);
+                advance(tile, blk);
+            }
+            tmem_st_wait();
+        };
+        // backward mode: the accumulators start at zero (every MMA accumulates; three warps issue, no MMA is "the first")
+        auto preload_zero = [&]() {
+            uint32_t r[32];
+#pragma unroll
+            for (int e = 0; e < 32; ++e) r[e] = 0u;
+            int tile = 0, blk = 0;
+            for (int item = 0; item < items; ++item) {
+                tmem_st32(tm_lane + tile * p.nb + (blk * 2 + half) * 32, r);
+                advance(tile, blk);
+            }
+            tmem_st_wait();
         };
         // hand-over to the MMA warp: in a pair the barrier lives in the leader CTA (the second CTA arrives remotely)
         const uint32_t r_acc_ready = PAIR ? mapa_u32(smem_u32(&acc_ready), 0) : 0u;
@@ -339,88 +359,93 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                         arrive_ready();
                     }
                     // backward: the ReLU mask of each item is compressed to one 32-bit word while the MMAs run
-                    uint32_t masks[8];
                     if (p.mode != 0) {
+                        int tile = 0, blk = 0;
+                        for (int item = 0; item < items; ++item) {
+                            int rho, rho_out, rho_m, c0; bool valid;
+                            row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
+                            uint32_t mbits = 0;
+                            if (valid) {
+                                const int chunk0 = (nbk * p.nb + c0) >> 3;
+                                uint4 mk[4];
 #pragma unroll
-                        for (int item = 0; item < 8; ++item) {
-                            masks[item] = 0;
-                            if (item < items) {
-                                int rho, rho_out, rho_m, tile, c0; bool valid;
-                                row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
-                                if (valid) {
-                                    const int chunk0 = (nbk * p.nb + c0) >> 3;
-                                    uint32_t mbits = 0;
+                                for (int g = 0; g < 4; ++g)
+                                    mk[g] = __ldg(reinterpret_cast<const uint4 *>(p.mask[l] + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
 #pragma unroll
-                                    for (int g = 0; g < 4; ++g) {
-                                        const uint4 mk = __ldg(reinterpret_cast<const uint4 *>(p.mask[l] + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
-                                        const uint32_t mw[4] = {mk.x, mk.y, mk.z, mk.w};
+                                for (int g = 0; g < 4; ++g) {
+                                    const uint32_t mw[4] = {mk[g].x, mk[g].y, mk[g].z, mk[g].w};
 #pragma unroll
-                                        for (int e = 0; e < 8; ++e) {
-                                            const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
-                                            // bf16 > 0  <=>  sign bit clear and not zero
-                                            if (h != 0 && (h & 0x8000u) == 0) mbits |= 1u << (g * 8 + e);
-                                        }
+                                    for (int e = 0; e < 8; ++e) {
+                                        const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                                        // bf16 > 0  <=>  sign bit clear and not zero
+                                        if (h != 0 && (h & 0x8000u) == 0) mbits |= 1u << (g * 8 + e);
                                     }
-                                    masks[item] = mbits;
                                 }
                             }
+                            mask_s[item][et] = mbits;
+                            advance(tile, blk);
                         }
                     }
-                    // inside a forward chain the next layer's bias is fetched one item ahead of the drain (the first item while
+                    // inside a forward chain the next layer's bias is fetched two items ahead of the drain (the first two while
                     // the MMAs still run) and written into each accumulator block right after that block has been drained
                     const bool bias_pipe = chain_more && p.mode == 0;
-                    uint4 bq[3][4];                                // bf16 bias of three items in flight: two ahead of the drain
-                    if (bias_pipe) { load_bias_item(0, l + 1, bq[0]); if (items > 1) load_bias_item(1, l + 1, bq[1]); }
+                    uint4 bq[3][4];                                // bf16 bias of three items in flight
+                    int ftile = 0, fblk = 0;                       // fetch cursor, two items ahead of the drain cursor
+                    if (bias_pipe) {
+                        load_bias_item(ftile, fblk, l + 1, 0, bq[0]); advance(ftile, fblk);
+                        if (items > 1) { load_bias_item(ftile, fblk, l + 1, 0, bq[1]); advance(ftile, fblk); }
+                    }
                     mbar_wait(&acc_full, a & 1);
                     tc_fence_after();
                     if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
                     if (threadIdx.x == 64 && pb == pos_first) CHAIN_STAMP(l, 2);
                     const int R_o = chain_more ? p.R_in : p.R_out;
+                    bf16 *out_pos = p.out[l] + (size_t)pos * chunks_out * R_o * 8;
+                    int tile = 0, blk = 0;                         // drain cursor
+                    for (int item0 = 0; item0 < items; item0 += 3) {
 #pragma unroll
-                    for (int item = 0; item < 8; ++item) {
-                        if (item >= items) break;
-                        int rho, rho_out, rho_m, tile, c0; bool valid;
-                        row_of(item, l, rho, rho_out, rho_m, valid, tile, c0);
-                        const int chunk0 = (nbk * p.nb + c0) >> 3;
-                        uint32_t r[32];
-                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
-                        if (bias_pipe && item + 2 < items) load_bias_item(item + 2, l + 1, bq[(item + 2) % 3]);
-                        tmem_ld_wait();
-                        if (valid) {
-                            const uint32_t mbits = masks[item];
+                        for (int u = 0; u < 3; ++u) {              // unrolled by the depth of the bias ring: static register indices
+                            const int item = item0 + u;
+                            if (item < items) {
+                                int rho, rho_out, rho_m, c0; bool valid;
+                                row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
+                                const int chunk0 = (nbk * p.nb + c0) >> 3;
+                                const uint32_t tm = tm_lane + tile * p.nb + c0;
+                                uint32_t r[32];
+                                tmem_ld32(tm, r);
+                                if (bias_pipe && item + 2 < items) { load_bias_item(ftile, fblk, l + 1, 0, bq[(u + 2) % 3]); advance(ftile, fblk); }
+                                const uint32_t mbits = p.mode != 0 ? mask_s[item][et] : 0u;
+                                tmem_ld_wait();
+                                if (valid) {
 #pragma unroll
-                            for (int g = 0; g < 4; ++g) {
-                                float v[8];
+                                    for (int g = 0; g < 4; ++g) {
+                                        float v[8];
 #pragma unroll
-                                for (int e = 0; e < 8; ++e) {
-                                    v[e] = __uint_as_float(r[g * 8 + e]);
-                                    if (p.mode == 0) v[e] = fmaxf(v[e], 0.f);
-                                    else if (!((mbits >> (g * 8 + e)) & 1u)) v[e] = 0.f;
+                                        for (int e = 0; e < 8; ++e) {
+                                            v[e] = __uint_as_float(r[g * 8 + e]);
+                                            if (p.mode == 0) v[e] = fmaxf(v[e], 0.f);
+                                            else if (!((mbits >> (g * 8 + e)) & 1u)) v[e] = 0.f;
+                                        }
+                                        uint4 o;
+                                        __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
+                                        __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
+                                        o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
+                                        o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
+                                        *reinterpret_cast<uint4 *>(out_pos + ((size_t)(chunk0 + g) * R_o + rho_out) * 8) = o;
+                                        if (chain_more) *reinterpret_cast<uint4 *>(img + ((size_t)(chunk0 + g) * p.R_in + rho) * 16) = o;
+                                    }
                                 }
-                                uint4 o;
-                                __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-                                __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
-                                o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
-                                o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
-                                *reinterpret_cast<uint4 *>(p.out[l] + (((size_t)pos * chunks_out + chunk0 + g) * R_o + rho_out) * 8) = o;
-                                if (chain_more) *reinterpret_cast<uint4 *>(img + ((size_t)(chunk0 + g) * p.R_in + rho) * 16) = o;
-                            }
-                        }
-                        if (chain_more && p.mode != 0) {
+                                if (chain_more && p.mode != 0) {
 #pragma unroll
-                            for (int e = 0; e < 32; ++e) r[e] = 0u;
-                            tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
-                        }
-                        if (bias_pipe) {
-                            const uint4 (&bb)[4] = bq[item % 3];
-#pragma unroll
-                            for (int g = 0; g < 4; ++g) {
-                                r[g * 8 + 0] = bb[g].x << 16; r[g * 8 + 1] = bb[g].x & 0xFFFF0000u;
-                                r[g * 8 + 2] = bb[g].y << 16; r[g * 8 + 3] = bb[g].y & 0xFFFF0000u;
-                                r[g * 8 + 4] = bb[g].z << 16; r[g * 8 + 5] = bb[g].z & 0xFFFF0000u;
-                                r[g * 8 + 6] = bb[g].w << 16; r[g * 8 + 7] = bb[g].w & 0xFFFF0000u;
+                                    for (int e = 0; e < 32; ++e) r[e] = 0u;
+                                    tmem_st32(tm, r);
+                                }
+                                if (bias_pipe) {
+                                    bias_to_f32(bq[u], r);
+                                    tmem_st32(tm, r);
+                                }
+                                advance(tile, blk);
                             }
-                            tmem_st32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.nb + c0, r);
                         }
                     }
                     if (chain_more) {
@@ -1243,7 +1268,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     static const bool want_pair = getenv("DG_PAIR") != nullptr;
     const bool pair = want_pair && cp.cout == cp.nb && cp.cin == cp.kp && cp.nb % 32 == 0 && cp.n >= 2;
     const size_t stage = (size_t)cp.kp * (pair ? cp.nb / 2 : cp.nb) * 2;
-    const size_t budget = 227 * 1024 - 1024;       // static smem (barriers) lives in the remaining KB
+    const size_t budget = 227 * 1024 - 14 * 1024;  // static smem (barriers, the epilogue's tables) lives in the remaining 14 KB
     DG_REQUIRE(img_bytes + 2 * stage <= budget, "bf16 path: image (%zu B) + weight ring do not fit shared memory", img_bytes);
     int ns = (int)((budget - img_bytes) / stage);
     if (ns > CONV_MAX_STAGES) ns = CONV_MAX_STAGES;
@@ -1393,9 +1418,9 @@ int dg_bf16_create(dg_model *m) {
     DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
     cudaEvent_t *evs[] = {&b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
     for (cudaEvent_t *e : evs) DG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
-    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-    DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 14 * 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 14 * 1024));
+    DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
     DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
     return 0;
 }

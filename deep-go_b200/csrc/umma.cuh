@@ -45,6 +45,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
 }
 // bounded wait: ~seconds at most, then trap
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+#pragma unroll 1
     for (uint32_t it = 0; it < (1u << 26); ++it)
         if (mbar_try_wait(bar, parity)) return;
     __trap();
