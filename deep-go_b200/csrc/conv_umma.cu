@@ -61,6 +61,7 @@ struct ConvParams {
 #define DBG_STAMP(slot) do { if (p.dbg) p.dbg[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
 __device__ __forceinline__ long long dg_globaltimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define CHAIN_STAMP(l, k) do { if (p.dbg && blockIdx.x == 0) p.dbg[148 * 10 + (l) * 4 + (k)] = clock64(); } while (0)
+#define CONV_BIAS_RING 6
 #define CONV_MAX_STAGES 8
 #define CONV_MAX_KPANELS 4
 
@@ -69,13 +70,13 @@ __device__ __forceinline__ long long dg_globaltimer() { long long t; asm volatil
 // issues the MMAs for both, the tensor cores share the weight halves.  Per SM that halves the weight bytes written into and
 // read out of shared memory -- the bandwidth that bounds the single-CTA kernel (87 instead of 65 cycles per MMA).
 #define CONV_MMA_WARPS 3
-template <bool PAIR>
+template <bool PAIR, int MODE>      // MODE 0: forward (bias + ReLU), 1: input gradient (ReLU mask of the layer's stored input)
 __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES], w_peer[CONV_MAX_STAGES];
     __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_peer, img_empty, acc_full, acc_ready;
     __shared__ uint32_t tmem_base_s;
-    __shared__ uint32_t row_s[4][256], mask_s[8][256];          // per-thread tables of the epilogue warps (see there)
+    __shared__ uint32_t row_s[4][256], mask_s[MODE == 1 ? 8 : 1][256];   // per-thread tables of the epilogue warps (see there)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
@@ -215,7 +216,6 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                     tc_fence_after();
                     if (lane == 0 && j == 0 && mma_id == 0) CHAIN_STAMP(l, 0);
                     uint32_t a_lo_k = a_lo_first;
-                    const uint32_t first_mma = 1u;                    // accumulators are pre-loaded (bias, or zeros in backward mode)
                     for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
                         if (l == 0 && nbk == 0) {
                             mbar_wait(&img_full[k], j & 1);
@@ -226,6 +226,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                         for (int ky = 0; ky < p.ksize; ++ky, a_lo_ky += p.pitch_in) {
                             for (int kx = 0; kx < p.ksize; ++kx) {
                                 const long long tw0 = p.dbg ? clock64() : 0;
+                                const bool first_stage = (k | ky | kx) == 0;      // the first MMA of a tile overwrites its accumulator
                                 wait_stage(s, ph);
                                 if (p.dbg) wait_cycles += clock64() - tw0;
                                 if (elect_one()) {
@@ -234,8 +235,9 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                                         const uint32_t d_tmem = tmem_base + (uint32_t)tile * p.nb;
 #pragma unroll 4
                                         for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep) {
-                                            if (PAIR) mma_bf16_pair(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma);
-                                            else mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, first_mma);
+                                            const uint32_t accumulate = first_stage ? (uint32_t)(ks != 0) : 1u;
+                                            if (PAIR) mma_bf16_pair(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, accumulate);
+                                            else mma_bf16(d_tmem, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, accumulate);
                                         }
                                     }
                                     if (PAIR) mma_commit_pair(&w_empty[s], 3); else mma_commit(&w_empty[s]);
@@ -291,57 +293,25 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
             rho_out = l == p.nchain - 1 ? (int)((ri >> 12) & 0xFFFu) : rho;
             rho_m = (int)(ri & 0xFFFu);
         };
-        auto bias_to_f32 = [&](const uint4 (&bq)[4], uint32_t (&r)[32]) {
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                r[g * 8 + 0] = bq[g].x << 16; r[g * 8 + 1] = bq[g].x & 0xFFFF0000u;        // bf16 -> fp32 bit patterns
-                r[g * 8 + 2] = bq[g].y << 16; r[g * 8 + 3] = bq[g].y & 0xFFFF0000u;
-                r[g * 8 + 4] = bq[g].z << 16; r[g * 8 + 5] = bq[g].z & 0xFFFF0000u;
-                r[g * 8 + 6] = bq[g].w << 16; r[g * 8 + 7] = bq[g].w & 0xFFFF0000u;
-            }
-        };
         // one item's bias (32 channels of one row) of layer l, N block nbk, into registers
         auto load_bias_item = [&](int tile, int blk, int l, int nbk, uint4 (&bq)[4]) {
             int rho, rho_out, rho_m, c0; bool valid;
             row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
             const int R_b = l == p.nchain - 1 ? p.R_out : p.R_in;
-            const int chunk0 = (nbk * p.nb + c0) >> 3;
+            const uint4 *src = reinterpret_cast<const uint4 *>(p.bias[l]) + (size_t)((nbk * p.nb + c0) >> 3) * R_b + rho_out;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int g = 0; g < 4; ++g, src += R_b) {
                 bq[g] = make_uint4(0u, 0u, 0u, 0u);
-                if (valid) bq[g] = __ldg(reinterpret_cast<const uint4 *>(p.bias[l] + ((size_t)(chunk0 + g) * R_b + rho_out) * 8));
+                if (valid) bq[g] = __ldg(src);
             }
-        };
-        // forward: accumulators start as bias[c] + a[c][x][y] (tcgen05.st), so the drain below has no global load
-        auto preload_bias = [&](int l, int nbk) {
-            int tile = 0, blk = 0;
-            for (int item = 0; item < items; ++item) {
-                uint4 bq[4];
-                uint32_t r[32];
-                load_bias_item(tile, blk, l, nbk, bq);
-                bias_to_f32(bq, r);
-                tmem_st32(tm_lane + tile * p.nb + (blk * 2 + half) * 32, r);
-                advance(tile, blk);
-            }
-            tmem_st_wait();
-        };
-        // backward mode: the accumulators start at zero (every MMA accumulates; three warps issue, no MMA is "the first")
-        auto preload_zero = [&]() {
-            uint32_t r[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) r[e] = 0u;
-            int tile = 0, blk = 0;
-            for (int item = 0; item < items; ++item) {
-                tmem_st32(tm_lane + tile * p.nb + (blk * 2 + half) * 32, r);
-                advance(tile, blk);
-            }
-            tmem_st_wait();
         };
         // hand-over to the MMA warp: in a pair the barrier lives in the leader CTA (the second CTA arrives remotely)
         const uint32_t r_acc_ready = PAIR ? mapa_u32(smem_u32(&acc_ready), 0) : 0u;
         auto arrive_ready = [&]() {
             if (lane == 0) { if (PAIR && rank == 1) mbar_arrive_remote(r_acc_ready); else mbar_arrive(&acc_ready); }
         };
+        const uint32_t img_s = smem_u32(img);
+        const uint32_t one2 = 0x3F803F80u;                         // bf16x2 {1, 1}
         uint32_t a = 0;
         for (int pb = pos_first; pb < p.n; pb += pos_step) {
             const int pos = pb + (int)rank;
@@ -351,34 +321,36 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
                     const bool chain_more = l + 1 < p.nchain;      // this layer's output is the next layer's shared-memory image
                     if (l == 0 || nnb > 1) {
-                        // first layer of a position (or a multi-N-block layer): hand the accumulators to the MMA warps here;
-                        // inside a chain the hand-over happens at the end of the previous layer's drain
-                        if (p.mode == 0) preload_bias(l, nbk); else preload_zero();
+                        // first layer of a position (or a multi-N-block layer): the accumulators are free (the first MMA of a tile
+                        // overwrites it); inside a chain the hand-over happens at the end of the previous layer's drain
                         tc_fence_before();
                         __syncwarp();
                         arrive_ready();
                     }
-                    // backward: the ReLU mask of each item is compressed to one 32-bit word while the MMAs run
-                    if (p.mode != 0) {
+                    // backward: while the MMAs run, the ReLU mask of each item (stored input of the layer > 0) is compressed to one
+                    // 32-bit word, laid out so that the drain expands it with byte permutes: element (chunk g, pair j, half h)
+                    // sits at the top of byte 2*(j&1)+h, shifted down by k = 2*g + (j>>1)
+                    if (MODE == 1) {
                         int tile = 0, blk = 0;
                         for (int item = 0; item < items; ++item) {
                             int rho, rho_out, rho_m, c0; bool valid;
                             row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
                             uint32_t mbits = 0;
                             if (valid) {
-                                const int chunk0 = (nbk * p.nb + c0) >> 3;
+                                const uint4 *src = reinterpret_cast<const uint4 *>(p.mask[l]) + ((size_t)pos * chunks_out + ((nbk * p.nb + c0) >> 3)) * p.R_mask + rho_m;
                                 uint4 mk[4];
 #pragma unroll
-                                for (int g = 0; g < 4; ++g)
-                                    mk[g] = __ldg(reinterpret_cast<const uint4 *>(p.mask[l] + (((size_t)pos * chunks_out + chunk0 + g) * p.R_mask + rho_m) * 8));
+                                for (int g = 0; g < 4; ++g) mk[g] = __ldg(src + (size_t)g * p.R_mask);
 #pragma unroll
                                 for (int g = 0; g < 4; ++g) {
                                     const uint32_t mw[4] = {mk[g].x, mk[g].y, mk[g].z, mk[g].w};
 #pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        const uint32_t h = (mw[e >> 1] >> ((e & 1) * 16)) & 0xFFFFu;
+                                    for (int j = 0; j < 4; ++j) {
+                                        const int k = 2 * g + (j >> 1);
                                         // bf16 > 0  <=>  sign bit clear and not zero
-                                        if (h != 0 && (h & 0x8000u) == 0) mbits |= 1u << (g * 8 + e);
+                                        const uint32_t lo = mw[j] & 0xFFFFu, hi = mw[j] >> 16;
+                                        if (lo != 0 && (lo & 0x8000u) == 0) mbits |= 1u << (8 * (2 * (j & 1)) + 7 - k);
+                                        if (hi != 0 && (hi & 0x8000u) == 0) mbits |= 1u << (8 * (2 * (j & 1) + 1) + 7 - k);
                                     }
                                 }
                             }
@@ -386,71 +358,75 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                             advance(tile, blk);
                         }
                     }
-                    // inside a forward chain the next layer's bias is fetched two items ahead of the drain (the first two while
-                    // the MMAs still run) and written into each accumulator block right after that block has been drained
-                    const bool bias_pipe = chain_more && p.mode == 0;
-                    uint4 bq[3][4];                                // bf16 bias of three items in flight
-                    int ftile = 0, fblk = 0;                       // fetch cursor, two items ahead of the drain cursor
-                    if (bias_pipe) {
-                        load_bias_item(ftile, fblk, l + 1, 0, bq[0]); advance(ftile, fblk);
-                        if (items > 1) { load_bias_item(ftile, fblk, l + 1, 0, bq[1]); advance(ftile, fblk); }
+                    // forward: the layer's bias (bf16, b[c] + a[c][x][y]) of the first CONV_BIAS_RING items is fetched while the MMAs
+                    // run; a slot is refilled (items beyond the ring) right after the drain has used it.  Loads inside the drain
+                    // queue behind its stores, so the ring is as deep as the registers allow.
+                    uint4 bq[MODE == 0 ? CONV_BIAS_RING : 1][4];
+                    int ftile = 0, fblk = 0;                       // fetch cursor
+                    if (MODE == 0) {
+#pragma unroll
+                        for (int u = 0; u < CONV_BIAS_RING; ++u)
+                            if (u < items) { load_bias_item(ftile, fblk, l, nbk, bq[u]); advance(ftile, fblk); }
                     }
                     mbar_wait(&acc_full, a & 1);
                     tc_fence_after();
                     if (a == 0 && threadIdx.x == 64) DBG_STAMP(5);
                     if (threadIdx.x == 64 && pb == pos_first) CHAIN_STAMP(l, 2);
                     const int R_o = chain_more ? p.R_in : p.R_out;
-                    bf16 *out_pos = p.out[l] + (size_t)pos * chunks_out * R_o * 8;
+                    uint4 *out_pos = reinterpret_cast<uint4 *>(p.out[l]) + (size_t)pos * chunks_out * R_o;
                     int tile = 0, blk = 0;                         // drain cursor
-                    for (int item0 = 0; item0 < items; item0 += 3) {
+                    for (int item0 = 0; item0 < items; item0 += CONV_BIAS_RING) {
 #pragma unroll
-                        for (int u = 0; u < 3; ++u) {              // unrolled by the depth of the bias ring: static register indices
+                        for (int u = 0; u < CONV_BIAS_RING; ++u) {   // unrolled by the ring depth: static register indices
                             const int item = item0 + u;
                             if (item < items) {
                                 int rho, rho_out, rho_m, c0; bool valid;
                                 row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
                                 const int chunk0 = (nbk * p.nb + c0) >> 3;
-                                const uint32_t tm = tm_lane + tile * p.nb + c0;
                                 uint32_t r[32];
-                                tmem_ld32(tm, r);
-                                if (bias_pipe && item + 2 < items) { load_bias_item(ftile, fblk, l + 1, 0, bq[(u + 2) % 3]); advance(ftile, fblk); }
-                                const uint32_t mbits = p.mode != 0 ? mask_s[item][et] : 0u;
+                                tmem_ld32(tm_lane + tile * p.nb + c0, r);
+                                const uint32_t mbits = MODE == 1 ? mask_s[item][et] : 0u;
                                 tmem_ld_wait();
                                 if (valid) {
+                                    uint4 *og = out_pos + (size_t)chunk0 * R_o + rho_out;
+                                    uint32_t sg = img_s + (uint32_t)(chunk0 * p.R_in + rho) * 16u;
 #pragma unroll
-                                    for (int g = 0; g < 4; ++g) {
-                                        float v[8];
+                                    for (int g = 0; g < 4; ++g, og += R_o, sg += (uint32_t)p.R_in * 16u) {
+                                        uint32_t w[4];
 #pragma unroll
-                                        for (int e = 0; e < 8; ++e) {
-                                            v[e] = __uint_as_float(r[g * 8 + e]);
-                                            if (p.mode == 0) v[e] = fmaxf(v[e], 0.f);
-                                            else if (!((mbits >> (g * 8 + e)) & 1u)) v[e] = 0.f;
+                                        for (int j = 0; j < 4; ++j) {
+                                            const __nv_bfloat162 t = __floats2bfloat162_rn(__uint_as_float(r[g * 8 + 2 * j]), __uint_as_float(r[g * 8 + 2 * j + 1]));
+                                            w[j] = *reinterpret_cast<const uint32_t *>(&t);
                                         }
-                                        uint4 o;
-                                        __nv_bfloat162 t0 = __floats2bfloat162_rn(v[0], v[1]), t1 = __floats2bfloat162_rn(v[2], v[3]);
-                                        __nv_bfloat162 t2 = __floats2bfloat162_rn(v[4], v[5]), t3 = __floats2bfloat162_rn(v[6], v[7]);
-                                        o.x = *reinterpret_cast<uint32_t *>(&t0); o.y = *reinterpret_cast<uint32_t *>(&t1);
-                                        o.z = *reinterpret_cast<uint32_t *>(&t2); o.w = *reinterpret_cast<uint32_t *>(&t3);
-                                        *reinterpret_cast<uint4 *>(out_pos + ((size_t)(chunk0 + g) * R_o + rho_out) * 8) = o;
-                                        if (chain_more) *reinterpret_cast<uint4 *>(img + ((size_t)(chunk0 + g) * p.R_in + rho) * 16) = o;
+                                        if (MODE == 0) {
+                                            // relu(acc + bias) on bf16 pairs: one packed fma per pair
+                                            const uint4 bb = bq[MODE == 0 ? u : 0][g];
+                                            const uint32_t bw[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+                                            for (int j = 0; j < 4; ++j) asm("fma.rn.relu.bf16x2 %0, %1, %2, %3;" : "=r"(w[j]) : "r"(w[j]), "r"(one2), "r"(bw[j]));
+                                        } else {
+                                            // each byte permute replicates two mask bits (byte tops) over a bf16 pair
+#pragma unroll
+                                            for (int hg = 0; hg < 2; ++hg) {
+                                                const uint32_t x = mbits << (2 * g + hg);
+                                                uint32_t m0, m1;
+                                                asm("prmt.b32 %0, %1, %1, 0x9988;" : "=r"(m0) : "r"(x));
+                                                asm("prmt.b32 %0, %1, %1, 0xBBAA;" : "=r"(m1) : "r"(x));
+                                                w[2 * hg] &= m0;
+                                                w[2 * hg + 1] &= m1;
+                                            }
+                                        }
+                                        *og = make_uint4(w[0], w[1], w[2], w[3]);
+                                        if (chain_more) asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sg), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
                                     }
                                 }
-                                if (chain_more && p.mode != 0) {
-#pragma unroll
-                                    for (int e = 0; e < 32; ++e) r[e] = 0u;
-                                    tmem_st32(tm, r);
-                                }
-                                if (bias_pipe) {
-                                    bias_to_f32(bq[u], r);
-                                    tmem_st32(tm, r);
-                                }
+                                if (MODE == 0 && item + CONV_BIAS_RING < items) { load_bias_item(ftile, fblk, l, nbk, bq[MODE == 0 ? u : 0]); advance(ftile, fblk); }
                                 advance(tile, blk);
                             }
                         }
                     }
                     if (chain_more) {
-                        // next layer: its accumulators (bias) and its input image are ready once every epilogue warp gets here
-                        tmem_st_wait();
+                        // next layer: the accumulators are free and its input image is complete once every epilogue warp gets here
                         fence_proxy_async();                       // generic-proxy st.shared -> visible to the tensor core's async proxy
                         tc_fence_before();
                         __syncwarp();
@@ -1268,7 +1244,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     static const bool want_pair = getenv("DG_PAIR") != nullptr;
     const bool pair = want_pair && cp.cout == cp.nb && cp.cin == cp.kp && cp.nb % 32 == 0 && cp.n >= 2;
     const size_t stage = (size_t)cp.kp * (pair ? cp.nb / 2 : cp.nb) * 2;
-    const size_t budget = 227 * 1024 - 14 * 1024;  // static smem (barriers, the epilogue's tables) lives in the remaining 14 KB
+    const size_t budget = 227 * 1024 - 15 * 1024;   // static smem (barriers, the epilogue's row table) lives in the remaining 8 KB
     DG_REQUIRE(img_bytes + 2 * stage <= budget, "bf16 path: image (%zu B) + weight ring do not fit shared memory", img_bytes);
     int ns = (int)((budget - img_bytes) / stage);
     if (ns > CONV_MAX_STAGES) ns = CONV_MAX_STAGES;
@@ -1277,8 +1253,10 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     int grid = cp.n < m->bf->num_sms ? cp.n : m->bf->num_sms;
     if (pair) grid = 2 * std::min((cp.n + 1) / 2, m->bf->num_sms / 2);
     { dg_prof_scope _ps(c, cp.mode ? DG_K_DGRAD : (cp.ksize == 5 || cp.cin < cp.cout ? DG_K_CONV_FIRST : DG_K_CONV));
-    if (pair) DG_CUDA(dg_launch_pdl(conv_umma_kernel<true>, dim3(grid), dim3(384), smem, c->stream, cp, 2));
-    else DG_CUDA(dg_launch_pdl(conv_umma_kernel<false>, dim3(grid), dim3(384), smem, c->stream, cp));
+    if (pair && cp.mode) DG_CUDA(dg_launch_pdl(conv_umma_kernel<true, 1>, dim3(grid), dim3(384), smem, c->stream, cp, 2));
+    else if (pair) DG_CUDA(dg_launch_pdl(conv_umma_kernel<true, 0>, dim3(grid), dim3(384), smem, c->stream, cp, 2));
+    else if (cp.mode) DG_CUDA(dg_launch_pdl(conv_umma_kernel<false, 1>, dim3(grid), dim3(384), smem, c->stream, cp));
+    else DG_CUDA(dg_launch_pdl(conv_umma_kernel<false, 0>, dim3(grid), dim3(384), smem, c->stream, cp));
     }
     c->launches++;
     if (timeline) {
@@ -1418,8 +1396,10 @@ int dg_bf16_create(dg_model *m) {
     DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
     cudaEvent_t *evs[] = {&b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
     for (cudaEvent_t *e : evs) DG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
-    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 14 * 1024));
-    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 14 * 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
+    DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
     DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
     DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
     return 0;

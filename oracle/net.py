@@ -82,7 +82,10 @@ def forward(flat, x, num_layers, channel_size, quant=None):
         bias = b.view(-1, 1, 1) + a                               # per-channel + per-point bias (experiments.lua:138,143-145)
         if i < len(layers) - 1:
             bias = _q(bias, quant)                                # the GPU's bf16 epilogue operand; the head keeps fp32
-        z = F.conv2d(h, Wq, None, padding=(k - 1) // 2) + bias.unsqueeze(0)
+        z = F.conv2d(h, Wq, None, padding=(k - 1) // 2)
+        if i < len(layers) - 1:
+            z = _q(z, quant)                                      # the GPU rounds the fp32 accumulator to bf16, then adds the
+        z = z + bias.unsqueeze(0)                                 # bf16 bias with one more rounding (packed fma + ReLU)
         zs.append(z)
         h = torch.relu(z)
         if i < len(layers) - 1:
