@@ -960,31 +960,35 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     HSTAMP(5);
 }
 
-// gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order
+// gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order.
+// A block owns 32 columns; its 8 warps take the positions n = w, w+8, .. and the partial sums meet in shared memory.
 __global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__restrict__ part, int n, int C, float *__restrict__ gW,
                                                                float *__restrict__ gb, float *__restrict__ ga) {
-    __shared__ float red[8];
+    __shared__ float red[8][32];
     const int width = 9 * C + DG_POINTS;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    float s0 = 0.f, s1 = 0.f;
+    const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + lane;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     if (i < width) {
-        int k = 0;
-        for (; k + 2 <= n; k += 2) { s0 += part[(size_t)k * width + i]; s1 += part[(size_t)(k + 1) * width + i]; }
-        if (k < n) s0 += part[(size_t)k * width + i];
+        int k = grp;
+        for (; k + 24 < n; k += 32) {
+            s0 += part[(size_t)k * width + i]; s1 += part[(size_t)(k + 8) * width + i];
+            s2 += part[(size_t)(k + 16) * width + i]; s3 += part[(size_t)(k + 24) * width + i];
+        }
+        for (; k < n; k += 8) s0 += part[(size_t)k * width + i];
     }
-    const float s = s0 + s1;
+    red[grp][lane] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (grp != 0) return;
+    float s = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) s += red[g][lane];
     float bsum = 0.f;
     if (i < 9 * C) gW[i] += s;
     else if (i < width) { ga[i - 9 * C] += s; bsum = s; }
 #pragma unroll
     for (int sh = 16; sh > 0; sh >>= 1) bsum += __shfl_xor_sync(0xffffffffu, bsum, sh);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = bsum;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float t = 0.f;
-        for (int w = 0; w < 8; ++w) t += red[w];
-        if (t != 0.f) atomicAdd(gb, t);                // at most two blocks hold bias-gradient elements
-    }
+    if (lane == 0 && bsum != 0.f) atomicAdd(gb, bsum);     // the conv bias of the head: a handful of blocks hold its 361 elements
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1506,12 +1510,6 @@ static int launch_head(dg_model *m, bool backward, float scale) {
         for (int i = 0; i < m->n; ++i) for (int k = 1; k < 6; ++k) d[k] += (double)(h[i * 8 + k] - h[i * 8]) / m->n;
         fprintf(stderr, "head timeline (cycles, mean over %d CTAs): image %.0f | logits %.0f | softmax %.0f | weight grad %.0f | input grad %.0f\n", m->n, d[1], d[2], d[3], d[4], d[5]);
     }
-    if (backward) {
-        dg_prof_scope _ps(c, DG_K_HEAD);
-        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 255) / 256, 256, 0, c->stream>>>(b->head_part, m->n, m->C, m->grads + li.offW,
-                                                                                         m->grads + li.offB, m->grads + li.offA);
-        c->launches++;
-    }
     DG_CUDA(cudaGetLastError());
     return 0;
 }
@@ -1556,11 +1554,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
     if (!b->deterministic) DG_CUDA(cudaMemsetAsync(b->gacc, 0, b->gacc_floats * 4, c->stream));
-    if (int rc = launch_head(m, true, scale)) return rc;
-    {
-        const LayerInfo &lh = m->layers[m->L - 1];
-        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads + lh.offW, lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS)) return rc;
-    }
+    if (int rc = launch_head(m, true, scale)) return rc;      // its per-position gradient partials are summed on the side stream
     // ---- input gradients first: dZ_{l} -> dZ_{l-1} for conv layers l = L-2 .. 1 (transposed conv with flipped taps, masked by
     // the ReLU of layer l's input h_l); with C <= 128 the whole chain is one kernel with dZ resident in shared memory
     {
@@ -1592,6 +1586,13 @@ int dg_bf16_backward(dg_model *m, float scale) {
     static long long *wdbg = nullptr;
     static const bool wtl = getenv("DG_TIMELINE") != nullptr;
     if (wtl && !wdbg) cudaMalloc(&wdbg, 148 * 8 * sizeof(long long));
+    {
+        const LayerInfo &lh = m->layers[m->L - 1];
+        dg_prof_scope _ps(c, DG_K_HEAD, b->side);
+        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, b->side>>>(b->head_part, m->n, m->C, m->grads + lh.offW,
+                                                                                       m->grads + lh.offB, m->grads + lh.offA);
+        c->launches++;
+    }
     // bias gradients of every conv layer: side stream, all dZ are ready
     for (int l = m->L - 2; l >= 0; --l) {
         const LayerInfo &li = m->layers[l];
@@ -1664,11 +1665,10 @@ int dg_bf16_backward(dg_model *m, float scale) {
     DG_CUDA(cudaEventRecord(b->ev_join, b->side));
     DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_join, 0));
     // data parallel: all weight gradients of the 3x3 layers become final together (one persistent launch), so the exchange
-    // is ONE allreduce of the conv layers' slice of the flat vector -- latency-optimal for 8.4 MB over NVLink; the small head
-    // bucket left earlier, right after the head kernel
+    // is ONE allreduce of the whole flat gradient vector -- latency-optimal for 8.4 MB over NVLink
     if (m->fused_step && c->world > 1) {
         const LayerInfo &l0 = m->layers[0], &lh = m->layers[m->L - 1];
-        if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW - l0.offW)) return rc;
+        if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS - l0.offW)) return rc;
     }
     DG_CUDA(cudaGetLastError());
     return 0;
