@@ -457,6 +457,7 @@ struct WgradParams {
     const bf16 *dz[WG_MAX_LAYERS];   // [n][cout/8][R][8]   (A, MN-major: M = cout channel)
     const bf16 *x[WG_MAX_LAYERS];    // [n][cin/8][R][8]    (B, MN-major: N = cin channel)
     float *gacc[WG_MAX_LAYERS];      // default path: fp32 accumulation buffer of the layer [tap][cin/4][cout][4], updated with 16-byte reductions
+    float *gab[WG_MAX_LAYERS];       // default path: bias-gradient accumulation buffer [(row - first)/4][cout][4] = sum over positions of dZ (or NULL)
     float *scratch;       // deterministic path (nl == 1, gacc[0] == NULL): partial tiles [combo][split][kx][nb/4][128][4]
     int nl;
     int n, cin, cout;     // cin padded (multiple of 16)
@@ -469,6 +470,7 @@ struct WgradParams {
 };
 
 #define WG_RP 128         // K rows per stage
+#define WG_PREFETCH 0     // units the L2 prefetch runs ahead of the panel ring
 
 __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -476,6 +478,10 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     // warps' MMAs of the next layer
     __shared__ uint64_t s_full[CONV_MAX_STAGES], s_empty[CONV_MAX_STAGES], acc_full[CONV_MMA_WARPS], acc_empty[CONV_MMA_WARPS];
     __shared__ uint32_t tmem_base_s;
+    // Bias gradients ride along: sum over positions of dZ = dZ^T x I, so one extra N = 16 MMA per 16 panel rows against a 16x16
+    // identity (MN-major, two 8-column chunks) accumulates this CTA's panel of the bias gradient in the spare TMEM columns.  The
+    // CTAs of one split (one per kernel row) share the dZ panel and take every ksize-th 16-row step each.
+    __shared__ __align__(128) uint16_t ident_s[2][16][8];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int combo = blockIdx.x / p.splits, split = blockIdx.x - combo * p.splits;
@@ -491,9 +497,16 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     const int chunks_dz = p.cout >> 3, chunks_x = p.cin >> 3;
     // channel chunks of dZ this M block really has (the rest of the 128 lanes accumulate garbage that is never stored)
     const int a_chunks = min(16, chunks_dz - mblk * 16);
+    const bool fused_bias = p.gab[0] != nullptr && nblk == 0;   // splits % panels == 0: every unit of this CTA is the same panel
+    const uint32_t bias_col = (uint32_t)p.ksize * p.nb;          // first spare TMEM column (ksize * nb + WG_RP <= 512)
 
     dg_pdl_launch_dependents();
     if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8] = clock64();
+    if (threadIdx.x < 256) {
+        const int ch = threadIdx.x >> 7, k = (threadIdx.x >> 3) & 15, e = threadIdx.x & 7;
+        ident_s[ch][k][e] = k == ch * 8 + e ? 0x3F80u : 0u;      // bf16 1.0
+    }
+    fence_proxy_async();
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], CONV_MMA_WARPS); }
         for (int w = 0; w < CONV_MMA_WARPS; ++w) { mbar_init(&acc_full[w], 1); mbar_init(&acc_empty[w], 8); }
@@ -512,10 +525,35 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         const int dpos = p.splits / panels, dpanel = p.splits - dpos * panels;
         const int brow_off = (ky - p.pad) * p.pitch - p.pad;
         const uint32_t tx = (uint32_t)a_chunks * WG_RP * 16 + (uint32_t)(p.nb >> 3) * rb * 16;
+        // L2 prefetch cursor, WG_PREFETCH units ahead of the ring: the panels come from HBM (the activations and dZ of 11 layers do
+        // not stay in L2) and three ring stages cannot cover that latency at the rate the MMAs consume them.  The CTAs of
+        // one split (one per kernel row ky) read the same dZ panel and overlapping x rows; each prefetches every ksize-th
+        // channel chunk of both, x with the row window of all kernel rows.
+        int f_li = 0, f_u = split, f_pos = pos0, f_panel = panel0;
+        const int xrows = WG_RP + 2 * p.pad * p.pitch + 2 * p.pad;
+        auto prefetch_next = [&]() {
+            if (f_li >= p.nl) return;
+            if (f_u < units) {
+                const int row0 = p.first + f_panel * WG_RP;
+                const uint8_t *asrc = (const uint8_t *)p.dz[f_li] + (((size_t)f_pos * chunks_dz + mblk * 16 + ky) * p.R + row0) * 16;
+                for (int c = ky; c < a_chunks; c += p.ksize, asrc += (size_t)p.ksize * p.R * 16) bulk_prefetch_l2(asrc, WG_RP * 16);
+                const uint8_t *bsrc = (const uint8_t *)p.x[f_li] + (((size_t)f_pos * chunks_x + nblk * (p.nb >> 3) + ky) * p.R + row0 - p.pad * p.pitch - p.pad) * 16;
+                for (int c = ky; c < (p.nb >> 3); c += p.ksize, bsrc += (size_t)p.ksize * p.R * 16) bulk_prefetch_l2(bsrc, (uint32_t)xrows * 16);
+            }
+            f_u += p.splits;
+            f_pos += dpos; f_panel += dpanel;
+            if (f_panel >= panels) { f_panel -= panels; ++f_pos; }
+            if (f_u >= units) { ++f_li; f_u = split; f_pos = pos0; f_panel = panel0; }
+        };
+        if (elect_one()) for (int i = 0; i < WG_PREFETCH; ++i) prefetch_next();
+        __syncwarp();
+        long long pw = 0, pi = 0;                                  // timeline: cycles waiting for a free stage / issuing copies
         for (int li = 0; li < p.nl; ++li) {
             int pos = pos0, panel = panel0;
             for (int u = split; u < units; u += p.splits) {
+                const long long t0 = p.dbg ? clock64() : 0;
                 mbar_wait(&s_empty[s], ph ^ 1);
+                const long long t1 = p.dbg ? clock64() : 0;
                 if (elect_one()) {
                     mbar_arrive_expect_tx(&s_full[s], tx);
                     uint8_t *sa = smem + (size_t)s * stage_bytes, *sb = sa + a_bytes;
@@ -526,13 +564,16 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                     const uint8_t *bsrc = (const uint8_t *)p.x[li] + (((size_t)pos * chunks_x + nblk * (p.nb >> 3)) * p.R + row0 + brow_off) * 16;
                     for (int c = 0; c < (p.nb >> 3); ++c, bsrc += (size_t)p.R * 16)
                         bulk_g2s(sb + (size_t)c * rb_pad * 16, bsrc, (uint32_t)rb * 16, &s_full[s]);
+                    if (WG_PREFETCH > 0) prefetch_next();
                 }
                 __syncwarp();
+                if (p.dbg) { const long long t2 = clock64(); pw += t1 - t0; pi += t2 - t1; }
                 if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
                 pos += dpos; panel += dpanel;
                 if (panel >= panels) { panel -= panels; ++pos; }
             }
         }
+        if (lane == 0 && p.dbg) { p.dbg[blockIdx.x * 8 + 5] = pw; p.dbg[blockIdx.x * 8 + 6] = pi; }
     } else if (warp == 1 || warp >= 10) {
         // three MMA warps: warp i issues the MMAs of kernel columns kx = i, i+3, .. (disjoint accumulators), so the shallow
         // tensor-pipe queue always has work while another warp waits on a panel barrier or commits (see conv_umma_kernel)
@@ -541,6 +582,8 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         const uint32_t hi_a = desc_hi(WG_RP * 16), hi_b = desc_hi((uint32_t)rb_pad * 16);
         const uint32_t a_lo_ring = desc_lo(smem_u32(smem), 128), b_lo_ring = desc_lo(smem_u32(smem) + a_bytes, 128);
         const uint32_t stage_units = stage_bytes >> 4;
+        const uint32_t idesc_bias = make_idesc_bf16(128, 16, 1, 1);
+        const uint64_t ident_desc = desc_join(desc_lo(smem_u32(ident_s), 128), desc_hi(16 * 16));
         uint32_t s = 0, ph = 0;
         uint32_t a_lo_s = a_lo_ring, b_lo_s = b_lo_ring;
         long long wcy = 0;
@@ -562,6 +605,9 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                         for (int ks = 0; ks < WG_RP / 16; ++ks, a_lo += 16, b_lo += 16)
                             mma_bf16(d_tmem, desc_join(a_lo, hi_a), desc_join(b_lo, hi_b), idesc, acc | (uint32_t)ks);
                     }
+                    if (fused_bias && mma_id == 0)
+                        for (int ks = ky; ks < WG_RP / 16; ks += p.ksize)
+                            mma_bf16(tmem_base + bias_col + 16u * ks, desc_join(a_lo_s + 16u * ks, hi_a), ident_desc, idesc_bias, acc);
                     mma_commit(&s_empty[s]);
                 }
                 __syncwarp();
@@ -614,6 +660,24 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                                                          : make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
+            if (w == 0 && fused_bias) {
+                // this CTA's share of the bias-gradient panel: 16-row steps ky, ky + ksize, .., alternating between the two warps of a lane quarter
+                const int panel = split % panels;
+                float4 *gb4 = reinterpret_cast<float4 *>(p.gab[li]);
+                for (int ks = ky + half * p.ksize; ks < WG_RP / 16; ks += 2 * p.ksize) {
+                    uint32_t r[32];
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + bias_col + 16u * ks, r);
+                    tmem_ld_wait();
+                    if (any && co < p.cout) {
+                        float4 *o = gb4 + (size_t)((panel * WG_RP + 16 * ks) >> 2) * p.cout + co;
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + (size_t)g * p.cout), "f"(__uint_as_float(r[g * 4])),
+                                         "f"(__uint_as_float(r[g * 4 + 1])), "f"(__uint_as_float(r[g * 4 + 2])), "f"(__uint_as_float(r[g * 4 + 3]))
+                                         : "memory");
+                    }
+                }
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[w]);
@@ -675,7 +739,10 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float *__restri
     }
 }
 
-struct FinalizeLayer { const float *gacc; float *gW; int cin_true, cin, cout, ksize; };
+struct FinalizeLayer {
+    const float *gacc; float *gW; int cin_true, cin, cout, ksize;
+    const float *gab; float *ga, *gb; int pitch, pad, first;      // bias gradients accumulated by the weight-gradient kernel (gab may be NULL)
+};
 
 // gW[(co*cin_true + ci)*KK + t] += gacc[t][ci/4][co][ci%4]: same tile transpose as above, one source instead of `splits`;
 // blockIdx.y selects the layer (one launch for the whole net when no per-layer gradient bucket is needed)
@@ -708,6 +775,30 @@ __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const FinalizeLayer
             }
         }
         __syncthreads();
+    }
+    // ga[c][p] += gab[(rho(p) - first)/4][c][..] ; gb[c] += sum_p of the same (nn.Add gradBias, conv gradBias)
+    if (fl.gab) {
+        float *red = &tile[0][0];
+        for (int c = blockIdx.x; c < cout; c += gridDim.x) {
+            float s = 0.f;
+            for (int pt = threadIdx.x; pt < DG_POINTS; pt += blockDim.x) {
+                const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
+                const int rr = (x + fl.pad) * fl.pitch + y + fl.pad - fl.first;
+                const float v = __ldg(fl.gab + ((size_t)(rr >> 2) * cout + c) * 4 + (rr & 3));
+                fl.ga[(size_t)c * DG_POINTS + pt] += v;
+                s += v;
+            }
+#pragma unroll
+            for (int sh = 16; sh > 0; sh >>= 1) s += __shfl_xor_sync(0xffffffffu, s, sh);
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                float t = 0.f;
+                for (int w = 0; w < 8; ++w) t += red[w];
+                fl.gb[c] += t;
+            }
+            __syncthreads();
+        }
     }
 }
 
@@ -1211,6 +1302,8 @@ struct Bf16Path {
     std::vector<FinalizeLayer> fin_host;
     float *gacc = nullptr;                 // weight-gradient accumulation buffers of all conv layers (default path)
     std::vector<size_t> gacc_off;          // per conv layer, in floats
+    std::vector<size_t> gab_off;           // bias-gradient accumulation buffers, same allocation
+    bool fused_bias = false;               // bias gradients come out of the weight-gradient kernel
     size_t gacc_floats = 0;
     bool deterministic = false;            // DG_DETERMINISTIC=1: partial tiles + ordered reduction instead of L2 reductions
     float *scratch = nullptr;              // weight-gradient partial tiles, two halves used alternately
@@ -1304,7 +1397,10 @@ static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const
     w.n_mblk = (cout + 127) / 128;
     w.combos = ksize * w.n_mblk * w.n_nblk;
     DG_REQUIRE(w.combos <= m->bf->num_sms, "bf16 path: too many weight-gradient tiles");
+    // a multiple of the panels per position: every CTA then sees one panel index only (its bias-gradient accumulator is one panel)
+    const int panels = g.ntiles * 128 / WG_RP;
     w.splits = m->bf->num_sms / w.combos;
+    if (w.splits > panels) w.splits -= w.splits % panels;
     const int rb_pad = (WG_RP + 2 * g.pad + 7) & ~7;
     const size_t stage = 16 * WG_RP * 16 + (size_t)(w.nb / 8) * rb_pad * 16;
     int ns = (int)((227 * 1024 - 1024) / stage);
@@ -1367,6 +1463,8 @@ int dg_bf16_create(dg_model *m) {
         for (int l = 0; l < L - 1; ++l) {
             const LayerInfo &li = m->layers[l];
             ft[l].gacc = nullptr; ft[l].gW = m->grads + li.offW; ft[l].cin_true = li.cin; ft[l].cin = b->ops[l].cin_pad; ft[l].cout = li.cout; ft[l].ksize = li.k;
+            const Geom &gl = l == 0 ? b->g_first : b->g3;
+            ft[l].gab = nullptr; ft[l].ga = m->grads + li.offA; ft[l].gb = m->grads + li.offB; ft[l].pitch = gl.pitch; ft[l].pad = gl.pad; ft[l].first = gl.first;
             (void)goff;
         }
         b->fin_host = ft;
@@ -1391,8 +1489,18 @@ int dg_bf16_create(dg_model *m) {
     b->deterministic = getenv("DG_DETERMINISTIC") != nullptr;
     b->gacc_off.assign(L - 1, 0);
     for (int l = 0; l < L - 1; ++l) { b->gacc_off[l] = b->gacc_floats; b->gacc_floats += (size_t)m->layers[l].k * m->layers[l].k * b->ops[l].cin_pad * m->layers[l].cout; }
+    // bias-gradient accumulation buffers behind them (same memset): the weight-gradient kernel needs the spare TMEM columns
+    b->gab_off.assign(L - 1, 0);
+    b->fused_bias = !b->deterministic;
+    for (int l = 0; l < L - 1; ++l) {
+        const Geom &gl = l == 0 ? b->g_first : b->g3;
+        WgradPlan wpl;
+        if (int rc = wgrad_plan(m, b->ops[l].cin_pad, m->layers[l].cout, m->layers[l].k, gl, wpl)) return rc;
+        if (m->layers[l].k * wpl.nb + WG_RP > 512 || wpl.splits % (gl.ntiles * 128 / WG_RP) != 0) b->fused_bias = false;
+        b->gab_off[l] = b->gacc_floats; b->gacc_floats += (size_t)gl.ntiles * 128 * m->layers[l].cout;
+    }
     DG_CUDA(cudaMalloc((void **)&b->gacc, b->gacc_floats * 4));
-    for (int l = 0; l < L - 1; ++l) b->fin_host[l].gacc = b->gacc + b->gacc_off[l];
+    for (int l = 0; l < L - 1; ++l) { b->fin_host[l].gacc = b->gacc + b->gacc_off[l]; b->fin_host[l].gab = b->fused_bias ? b->gacc + b->gab_off[l] : nullptr; }
     DG_CUDA(cudaMemcpyAsync(b->fin_table, b->fin_host.data(), b->fin_host.size() * sizeof(FinalizeLayer), cudaMemcpyHostToDevice, st));
     DG_CUDA(cudaStreamSynchronize(st));
     DG_CUDA(cudaMalloc((void **)&b->scratch, 2 * scratch));
@@ -1594,7 +1702,8 @@ int dg_bf16_backward(dg_model *m, float scale) {
         c->launches++;
     }
     // bias gradients of every conv layer: side stream, all dZ are ready
-    for (int l = m->L - 2; l >= 0; --l) {
+    static const bool exp_nobias = getenv("DG_EXP_NOBIAS") != nullptr;
+    for (int l = m->L - 2; l >= 0 && !exp_nobias && !b->fused_bias; --l) {
         const LayerInfo &li = m->layers[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
         const int groups = m->n >= 64 ? 32 : (m->n >= 8 ? 8 : 1);
@@ -1620,6 +1729,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
             wp.dz[j] = b->dzl[l - j];
             wp.x[j] = (l - j) == 0 ? b->x0 : b->h[l - j];
             wp.gacc[j] = b->deterministic ? nullptr : b->gacc + b->gacc_off[l - j];
+            wp.gab[j] = b->fused_bias ? b->gacc + b->gab_off[l - j] : nullptr;
         }
         wp.scratch = scratch; wp.nl = nl;
         wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
@@ -1636,9 +1746,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
             std::vector<long long> h(148 * 8);
             cudaStreamSynchronize(c->stream);
             cudaMemcpy(h.data(), wp.dbg, h.size() * 8, cudaMemcpyDeviceToHost);
-            double d1 = 0, d2 = 0, d3 = 0, d4 = 0; const int gsz = w.combos * w.splits;
-            for (int i = 0; i < gsz; ++i) { d1 += (double)(h[i * 8 + 1] - h[i * 8]) / gsz; d2 += (double)(h[i * 8 + 2] - h[i * 8]) / gsz; d3 += (double)h[i * 8 + 3] / gsz; d4 += (double)(h[i * 8 + 4] - h[i * 8]) / gsz; }
-            fprintf(stderr, "wgrad timeline (cycles, mean over %d CTAs) k=%d layers=%d: mma loop start %.0f end %.0f (waiting for panels %.0f) | CTA end %.0f\n", gsz, li.k, nl, d1, d2, d3, d4);
+            double d1 = 0, d2 = 0, d3 = 0, d4 = 0, d5 = 0, d6 = 0; const int gsz = w.combos * w.splits;
+            for (int i = 0; i < gsz; ++i) { d1 += (double)(h[i * 8 + 1] - h[i * 8]) / gsz; d2 += (double)(h[i * 8 + 2] - h[i * 8]) / gsz; d3 += (double)h[i * 8 + 3] / gsz; d4 += (double)(h[i * 8 + 4] - h[i * 8]) / gsz; d5 += (double)h[i * 8 + 5] / gsz; d6 += (double)h[i * 8 + 6] / gsz; }
+            fprintf(stderr, "wgrad timeline (cycles, mean over %d CTAs) k=%d layers=%d: mma loop start %.0f end %.0f (waiting for panels %.0f) | CTA end %.0f | producer: waiting for a free stage %.0f, issuing copies %.0f\n", gsz, li.k, nl, d1, d2, d3, d4, d5, d6);
         }
         DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
         DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));

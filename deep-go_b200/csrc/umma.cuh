@@ -59,6 +59,11 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32
                  : "memory");
 }
 
+// pull `bytes` (multiple of 16) at src into L2 ahead of a later bulk copy
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
 // ---- thread-block cluster / CTA pair (cta_group::2) -------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void cluster_sync_all() {
