@@ -466,11 +466,11 @@ struct WgradParams {
     int n_mblk, n_nblk;   // cout / 128 (rounded up), cin / nb
     int splits;           // split-K CTAs per combo
     int nstages;
+    int ngroups;          // CTAs are dealt to `ngroups` layer groups: group g walks layers g, g + ngroups, .. with `splits` CTAs per kernel row
     long long *dbg;       // optional timeline (DG_TIMELINE=1): per CTA {start, mma-loop start, mma-loop end, total wait, end}
 };
 
 #define WG_RP 128         // K rows per stage
-#define WG_PREFETCH 0     // units the L2 prefetch runs ahead of the panel ring
 
 __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -484,7 +484,10 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     __shared__ __align__(128) uint16_t ident_s[2][16][8];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int combo = blockIdx.x / p.splits, split = blockIdx.x - combo * p.splits;
+    // Fewer, longer split-K runs per layer: with G layer groups a CTA accumulates G times more units in TMEM before it drains, so
+    // the accumulator hand-over (and the L2 reduction traffic) is paid 1/G as often.
+    const int grp = blockIdx.x % p.ngroups, bidx = blockIdx.x / p.ngroups;
+    const int combo = bidx / p.splits, split = bidx - combo * p.splits;
     // combo -> (ky, mblk, nblk)
     const int nblk = combo % p.n_nblk, mblk = (combo / p.n_nblk) % p.n_mblk, ky = combo / (p.n_nblk * p.n_mblk);
     const int rb = WG_RP + 2 * p.pad;                         // B panel rows incl. the kx halo
@@ -525,30 +528,8 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         const int dpos = p.splits / panels, dpanel = p.splits - dpos * panels;
         const int brow_off = (ky - p.pad) * p.pitch - p.pad;
         const uint32_t tx = (uint32_t)a_chunks * WG_RP * 16 + (uint32_t)(p.nb >> 3) * rb * 16;
-        // L2 prefetch cursor, WG_PREFETCH units ahead of the ring: the panels come from HBM (the activations and dZ of 11 layers do
-        // not stay in L2) and three ring stages cannot cover that latency at the rate the MMAs consume them.  The CTAs of
-        // one split (one per kernel row ky) read the same dZ panel and overlapping x rows; each prefetches every ksize-th
-        // channel chunk of both, x with the row window of all kernel rows.
-        int f_li = 0, f_u = split, f_pos = pos0, f_panel = panel0;
-        const int xrows = WG_RP + 2 * p.pad * p.pitch + 2 * p.pad;
-        auto prefetch_next = [&]() {
-            if (f_li >= p.nl) return;
-            if (f_u < units) {
-                const int row0 = p.first + f_panel * WG_RP;
-                const uint8_t *asrc = (const uint8_t *)p.dz[f_li] + (((size_t)f_pos * chunks_dz + mblk * 16 + ky) * p.R + row0) * 16;
-                for (int c = ky; c < a_chunks; c += p.ksize, asrc += (size_t)p.ksize * p.R * 16) bulk_prefetch_l2(asrc, WG_RP * 16);
-                const uint8_t *bsrc = (const uint8_t *)p.x[f_li] + (((size_t)f_pos * chunks_x + nblk * (p.nb >> 3) + ky) * p.R + row0 - p.pad * p.pitch - p.pad) * 16;
-                for (int c = ky; c < (p.nb >> 3); c += p.ksize, bsrc += (size_t)p.ksize * p.R * 16) bulk_prefetch_l2(bsrc, (uint32_t)xrows * 16);
-            }
-            f_u += p.splits;
-            f_pos += dpos; f_panel += dpanel;
-            if (f_panel >= panels) { f_panel -= panels; ++f_pos; }
-            if (f_u >= units) { ++f_li; f_u = split; f_pos = pos0; f_panel = panel0; }
-        };
-        if (elect_one()) for (int i = 0; i < WG_PREFETCH; ++i) prefetch_next();
-        __syncwarp();
         long long pw = 0, pi = 0;                                  // timeline: cycles waiting for a free stage / issuing copies
-        for (int li = 0; li < p.nl; ++li) {
+        for (int li = grp; li < p.nl; li += p.ngroups) {
             int pos = pos0, panel = panel0;
             for (int u = split; u < units; u += p.splits) {
                 const long long t0 = p.dbg ? clock64() : 0;
@@ -564,7 +545,6 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                     const uint8_t *bsrc = (const uint8_t *)p.x[li] + (((size_t)pos * chunks_x + nblk * (p.nb >> 3)) * p.R + row0 + brow_off) * 16;
                     for (int c = 0; c < (p.nb >> 3); ++c, bsrc += (size_t)p.R * 16)
                         bulk_g2s(sb + (size_t)c * rb_pad * 16, bsrc, (uint32_t)rb * 16, &s_full[s]);
-                    if (WG_PREFETCH > 0) prefetch_next();
                 }
                 __syncwarp();
                 if (p.dbg) { const long long t2 = clock64(); pw += t1 - t0; pi += t2 - t1; }
@@ -588,8 +568,8 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         uint32_t a_lo_s = a_lo_ring, b_lo_s = b_lo_ring;
         long long wcy = 0;
         if (lane == 0 && p.dbg && mma_id == 0) p.dbg[blockIdx.x * 8 + 1] = clock64();
-        for (int li = 0; li < p.nl; ++li) {
-            mbar_wait(&acc_empty[mma_id], (li & 1) ^ 1);      // the drain warps have read this warp's accumulators of the previous layer
+        for (int li = grp, lc = 0; li < p.nl; li += p.ngroups, ++lc) {
+            mbar_wait(&acc_empty[mma_id], (lc & 1) ^ 1);      // the drain warps have read this warp's accumulators of the previous layer
             tc_fence_after();
             uint32_t acc = 0;
             for (int u = split; u < units; u += p.splits) {
@@ -625,12 +605,12 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
         const bool any = split < units;                       // a CTA without units holds an unwritten accumulator
         const int co = mblk * 128 + q * 32 + lane;
         const int cin4 = p.cin >> 2;
-        for (int li = 0; li < p.nl; ++li) {
+        for (int li = grp, lc = 0; li < p.nl; li += p.ngroups, ++lc) {
             float4 *gl = reinterpret_cast<float4 *>(p.gacc[li]);
             // scratch tile layout [kx][ci/4][co][4]: lane = co, so one warp-wide 16-byte access covers 512 contiguous bytes
             float4 *sc = reinterpret_cast<float4 *>(p.scratch) + ((size_t)combo * p.splits + split) * p.ksize * 32 * p.nb + (q * 32 + lane);
             for (int w = 0; w < CONV_MMA_WARPS; ++w) {
-            mbar_wait(&acc_full[w], li & 1);
+            mbar_wait(&acc_full[w], lc & 1);
             tc_fence_after();
             for (int kx = w; kx < p.ksize; kx += CONV_MMA_WARPS)
                 for (int c0 = half * 32; c0 < p.nb; c0 += 64) {
@@ -1702,8 +1682,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         c->launches++;
     }
     // bias gradients of every conv layer: side stream, all dZ are ready
-    static const bool exp_nobias = getenv("DG_EXP_NOBIAS") != nullptr;
-    for (int l = m->L - 2; l >= 0 && !exp_nobias && !b->fused_bias; --l) {
+    for (int l = m->L - 2; l >= 0 && !b->fused_bias; --l) {
         const LayerInfo &li = m->layers[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
         const int groups = m->n >= 64 ? 32 : (m->n >= 8 ? 8 : 1);
@@ -1734,7 +1713,11 @@ int dg_bf16_backward(dg_model *m, float scale) {
         wp.scratch = scratch; wp.nl = nl;
         wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
         wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
-        wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
+        // two layer groups when the layers and the splits divide evenly (the per-CTA panel index must stay fixed for the bias gradient)
+        const int panels_l = g.ntiles * 128 / WG_RP;
+        const int ngroups = (!b->deterministic && nl % 2 == 0 && w.splits % (2 * panels_l) == 0 && m->n * panels_l >= w.splits) ? 2 : 1;
+        wp.ngroups = ngroups;
+        wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits / ngroups; wp.nstages = w.nstages;
         wp.dbg = wtl ? wdbg : nullptr;
         // deterministic path: this scratch half was last read by the reduction two layers ago
         if (b->deterministic && rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));

@@ -69,8 +69,19 @@ static void run(const char *name, RCfg c, int grid) {
     cudaFree(d);
 }
 
-int main() {
+int main(int argc, char **argv) {
     const int R = 432;
+    if (argc > 1) {
+        // weight-gradient operand geometry: MN-major, chunk stride (SBO) = rows per stage x 16 B, with and without one row of padding
+        for (int grid : {1, 148})
+            for (int a_rows : {128, 129, 132, 136})
+                for (int b_rows : {136, 137, 140, 132}) {
+                    RCfg m = {128, 512, 3, 1, 1, 0, 128, a_rows * 16, 128, b_rows * 16, 256, 256, 8, 8};
+                    char nm[96]; snprintf(nm, sizeof nm, "MN-major N=128 3 acc, A chunk stride %d B, B chunk stride %d B", a_rows * 16, b_rows * 16);
+                    run(nm, m, grid);
+                }
+        return 0;
+    }
     // K-major no-swizzle blocked image: LBO = R*16 (chunk stride), SBO = 128, k-step = 2 chunks
     RCfg k128 = {128, 512, 1, 0, 0, 0, R * 16, 128, 128 * 16, 128, 2 * R * 16, 2 * 128 * 16, 4, 4};
     for (int grid : {1, 148}) {
