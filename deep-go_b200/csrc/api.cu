@@ -40,6 +40,12 @@ extern "C" int dg_ctx_create(int device, dg_ctx **out) {
     dg_ctx *c = new dg_ctx();
     c->dev = device;
     DG_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    if (getenv("DG_TL")) {
+        unsigned long long h[3 * DG_TL_COUNT];
+        for (int i = 0; i < 3 * DG_TL_COUNT; ++i) h[i] = (i % 3 == 2) ? 0ull : ~0ull;
+        DG_CUDA(cudaMalloc((void **)&c->tl, sizeof(h)));
+        DG_CUDA(cudaMemcpy(c->tl, h, sizeof(h), cudaMemcpyHostToDevice));
+    }
     DG_CUDA(cudaEventCreate(&c->t0));
     DG_CUDA(cudaEventCreate(&c->t1));
     *out = c;
@@ -107,6 +113,19 @@ extern "C" int dg_prof_get(dg_ctx *c, int kind, float *ms_total, long long *laun
     DG_REQUIRE(c && kind >= 0 && kind < DG_K_COUNT, "dg_prof_get: bad argument");
     if (ms_total) *ms_total = (float)c->prof_ms[kind];
     if (launches) *launches = c->prof_n[kind];
+    return 0;
+}
+
+extern "C" int dg_prof_timeline(dg_ctx *c, unsigned long long *out, int n) {
+    DG_REQUIRE(c && out && n >= 0, "dg_prof_timeline: bad argument");
+    DG_REQUIRE(c->tl, "dg_prof_timeline: start the process with DG_TL=1");
+    DG_CUDA(cudaSetDevice(c->dev));
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    unsigned long long h[3 * DG_TL_COUNT];
+    DG_CUDA(cudaMemcpy(h, c->tl, sizeof(h), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n && i < 3 * DG_TL_COUNT; ++i) out[i] = h[i];
+    for (int i = 0; i < 3 * DG_TL_COUNT; ++i) h[i] = (i % 3 == 2) ? 0ull : ~0ull;
+    DG_CUDA(cudaMemcpy(c->tl, h, sizeof(h), cudaMemcpyHostToDevice));
     return 0;
 }
 
@@ -292,6 +311,7 @@ extern "C" int dg_model_get_grads(dg_model *m, float *host, size_t n) {
     DG_REQUIRE(m && host, "dg_model_get_grads: NULL argument");
     DG_REQUIRE(n == m->P, "dg_model_get_grads: buffer holds %zu values, the model has %zu parameters", n, m->P);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (m->bf) if (int rc = dg_bf16_sync_grads(m)) return rc;
     DG_CUDA(cudaMemcpyAsync(host, m->grads, n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
     DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
     return 0;
@@ -299,6 +319,7 @@ extern "C" int dg_model_get_grads(dg_model *m, float *host, size_t n) {
 extern "C" int dg_zero_grads(dg_model *m) {
     DG_REQUIRE(m, "dg_zero_grads: model is NULL");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (m->bf) dg_bf16_drop_pending_grads(m);
     DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, m->ctx->stream));
     return 0;
 }
@@ -429,6 +450,7 @@ extern "C" int dg_forward(dg_model *m, float *logprobs_out) {
 extern "C" int dg_loss_backward(dg_model *m, float *loss_out) {
     DG_REQUIRE(m, "dg_loss_backward: model is NULL");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (m->bf) if (int rc = dg_bf16_sync_grads(m)) return rc;      // this call accumulates into the gradient vector
     if (int rc = backward_impl(m)) return rc;
     if (loss_out) return read_loss(m, loss_out, nullptr);
     return 0;
@@ -437,14 +459,21 @@ extern "C" int dg_loss_backward(dg_model *m, float *loss_out) {
 extern "C" int dg_sgd_step(dg_model *m, float rate) {
     DG_REQUIRE(m, "dg_sgd_step: model is NULL");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
-    if (m->bf) return dg_bf16_sgd_step(m, rate, nullptr);
+    if (m->bf) { if (int rc = dg_bf16_sync_grads(m)) return rc; return dg_bf16_sgd_step(m, rate, nullptr); }
     return dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate);
 }
 
 // one fused step on the context's stream: eval() of train.lua:4-12 followed by SGD:step (train.lua:131)
 static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
     dg_ctx *c = m->ctx;
-    DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));          // train.lua:5
+    static const bool exp_fullmemset = getenv("DG_EXP_FULLMEMSET") != nullptr;
+    if (m->bf && dg_bf16_defers_grads(m) && !exp_fullmemset) {
+        // the conv layers' gradient goes from the accumulation buffers straight into the SGD kernel: only the head's slice is summed in place
+        const LayerInfo &lh = m->layers[m->L - 1];
+        DG_CUDA(cudaMemsetAsync(m->grads + lh.offW, 0, (m->P - lh.offW) * 4, c->stream));
+    } else {
+        DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));      // train.lua:5
+    }
     m->fused_step = true;
     int rc = forward_impl(m);                                              // train.lua:6
     if (!rc) rc = backward_impl(m);                                        // train.lua:8-10
@@ -478,6 +507,7 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
             cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
             if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
             DG_REQUIRE(e == cudaSuccess && graph, "dg_train_step: graph capture failed: %s", cudaGetErrorString(e));
+            if (const char *dot = getenv("DG_GRAPH_DOT")) cudaGraphDebugDotPrint(graph, dot, 0);     // dev aid: the captured step as graphviz
             e = cudaGraphInstantiate(&m->step_graph, graph, 0);
             cudaGraphDestroy(graph);
             DG_REQUIRE(e == cudaSuccess, "dg_train_step: cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
@@ -487,6 +517,7 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
         }
         DG_CUDA(cudaGraphLaunch(m->step_graph, c->stream));
         c->launches += m->step_graph_launches;
+        dg_bf16_after_fused_step(m);
         m->forward_done = true;
     } else {
         if (int rc = train_step_body(m, rate, false)) return rc;
@@ -498,6 +529,7 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
 extern "C" int dg_dp_allreduce_grads(dg_model *m) {
     DG_REQUIRE(m, "dg_dp_allreduce_grads: model is NULL");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
+    if (m->bf) if (int rc = dg_bf16_sync_grads(m)) return rc;
     if (int rc = dg_dp_bucket(m->ctx, m->grads, m->P)) return rc;
     return dg_dp_finish(m->ctx);
 }

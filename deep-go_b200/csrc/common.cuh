@@ -60,7 +60,11 @@ struct dg_ctx {
     int rank = 0, world = 1;
     cudaStream_t comm_stream = nullptr;
     cudaEvent_t ev_grad_ready = nullptr, ev_comm_done = nullptr;
+    // DG_TL=1: device buffer of globaltimer stamps {first CTA in, first CTA past the dependency wait, last CTA out} per kernel of the
+    // step -- the only clock that sees inside a replayed CUDA graph (dg_prof_timeline)
+    unsigned long long *tl = nullptr;
 };
+enum { DG_TL_CONV0 = 0, DG_TL_CONV, DG_TL_HEAD, DG_TL_DGRAD, DG_TL_WGRAD, DG_TL_WGRAD0, DG_TL_FINALIZE, DG_TL_SGD, DG_TL_HEADRED, DG_TL_COUNT };
 
 struct LayerInfo {
     int cin, cout, k;
@@ -75,6 +79,10 @@ int dg_ctx_scratch(dg_ctx *ctx, size_t bytes, void **out);
 #ifdef __CUDACC__
 __device__ __forceinline__ void dg_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void dg_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ unsigned long long dg_gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define DG_TL_IN(tl, id) do { if ((tl) && threadIdx.x == 0) atomicMin((tl) + 3 * (id), dg_gtimer()); } while (0)
+#define DG_TL_GO(tl, id) do { if ((tl) && threadIdx.x == 0) atomicMin((tl) + 3 * (id) + 1, dg_gtimer()); } while (0)
+#define DG_TL_OUT(tl, id) do { if ((tl) && threadIdx.x == 0) atomicMax((tl) + 3 * (id) + 2, dg_gtimer()); } while (0)
 template <typename... KArgs, typename... Args>
 static inline cudaError_t dg_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
     cudaLaunchConfig_t cfg = {};
@@ -82,7 +90,8 @@ static inline cudaError_t dg_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = 1;
+    static const bool no_pdl = getenv("DG_NO_PDL") != nullptr;
+    cfg.attrs = at; cfg.numAttrs = no_pdl ? 0 : 1;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 // same, as thread-block clusters of `cluster` CTAs along x (grid.x must be a multiple of it)

@@ -48,6 +48,7 @@ struct ConvParams {
     const bf16 *mask[CONV_MAX_CHAIN];  // mode 1: [n][cout/8][R_mask][8], output kept where mask > 0
     int nchain;
     int n, cin, cout;
+    unsigned long long *tl; int tl_id;
     int R_in, pitch_in, pad_in, ksize, first, ntiles;
     int R_out, pitch_out, pad_out;     // geometry of the LAST layer's HBM output (intermediate layers: same as the input)
     int R_mask, pitch_mask, pad_mask;
@@ -95,6 +96,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
     const int pos_step = PAIR ? (int)(gridDim.x & ~1u) : (int)gridDim.x;
 
     dg_pdl_launch_dependents();
+    DG_TL_IN(p.tl, p.tl_id);
     if (threadIdx.x == 0) {
         DBG_STAMP(0);
         for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], CONV_MMA_WARPS); mbar_init(&w_peer[s], 1); }
@@ -114,6 +116,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
     dg_pdl_wait();                 // everything above overlapped the previous kernel's tail; its output is visible from here on
+    DG_TL_GO(p.tl, p.tl_id);
     if (threadIdx.x == 0) { DBG_STAMP(1); if (p.dbg) p.dbg[148 * 8 + blockIdx.x * 2] = dg_globaltimer(); }
 
     if (warp == 0) {
@@ -443,6 +446,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
     tc_fence_before();
     if (PAIR) cluster_sync_all(); else __syncthreads();          // a pair: neither CTA may leave while the other still uses its memory
     if (warp == 1) { if (PAIR) tmem_dealloc2(tmem_base, 512); else tmem_dealloc(tmem_base, 512); }
+    DG_TL_OUT(p.tl, p.tl_id);
     if (threadIdx.x == 0 && p.dbg) p.dbg[148 * 8 + blockIdx.x * 2 + 1] = dg_globaltimer();
 }
 
@@ -466,6 +470,7 @@ struct WgradParams {
     int n_mblk, n_nblk;   // cout / 128 (rounded up), cin / nb
     int splits;           // split-K CTAs per combo
     int nstages;
+    unsigned long long *tl; int tl_id;
     int ngroups;          // CTAs are dealt to `ngroups` layer groups: group g walks layers g, g + ngroups, .. with `splits` CTAs per kernel row
     long long *dbg;       // optional timeline (DG_TIMELINE=1): per CTA {start, mma-loop start, mma-loop end, total wait, end}
 };
@@ -504,6 +509,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     const uint32_t bias_col = (uint32_t)p.ksize * p.nb;          // first spare TMEM column (ksize * nb + WG_RP <= 512)
 
     dg_pdl_launch_dependents();
+    DG_TL_IN(p.tl, p.tl_id);
     if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8] = clock64();
     if (threadIdx.x < 256) {
         const int ch = threadIdx.x >> 7, k = (threadIdx.x >> 3) & 15, e = threadIdx.x & 7;
@@ -521,6 +527,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
     dg_pdl_wait();
+    DG_TL_GO(p.tl, p.tl_id);
 
     if (warp == 0) {
         uint32_t s = 0, ph = 0;
@@ -667,6 +674,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, 512);
+    DG_TL_OUT(p.tl, p.tl_id);
     if (threadIdx.x == 0 && p.dbg) p.dbg[blockIdx.x * 8 + 4] = clock64();
 }
 
@@ -724,41 +732,48 @@ struct FinalizeLayer {
     const float *gab; float *ga, *gb; int pitch, pad, first;      // bias gradients accumulated by the weight-gradient kernel (gab may be NULL)
 };
 
-// gW[(co*cin_true + ci)*KK + t] += gacc[t][ci/4][co][ci%4]: same tile transpose as above, one source instead of `splits`;
-// blockIdx.y selects the layer (one launch for the whole net when no per-layer gradient bucket is needed)
-__global__ void __launch_bounds__(256) wgrad_finalize_kernel(const FinalizeLayer *__restrict__ table) {
-    __shared__ float tile[64][17];
+// gW[(co*cin_true + ci)*KK + t] += gacc[t][ci/4][co][ci%4].  blockIdx.y selects the layer (one launch for the whole net).  A tile is
+// (co_t output channels) x (16 input channels) x ALL taps: the accumulation buffer is read with co-fastest 16-byte loads, and
+// each output channel's 16*KK gradient elements are contiguous in the Torch7 order, so the read-modify-write of gW is coalesced
+// and touches every sector once (a tile per tap wrote 4 of every 36 bytes, nine times over).
+#define FIN_SMEM_FLOATS (16 * (16 * 9 + 1))
+__global__ void __launch_bounds__(256) wgrad_finalize_kernel(const FinalizeLayer *__restrict__ table, unsigned long long *tl) {
+    extern __shared__ float tile[];
+    DG_TL_IN(tl, DG_TL_FINALIZE);                  // [co_t][16 * KK + 1]
     const FinalizeLayer fl = table[blockIdx.y];
     const float *__restrict__ gacc = fl.gacc;
     float *__restrict__ gW = fl.gW;
     const int cin_true = fl.cin_true, cin = fl.cin, cout = fl.cout, ksize = fl.ksize;
     const int KK = ksize * ksize, cin4 = cin >> 2;
-    const int co_tiles = (cout + 63) >> 6, ci_tiles = cin >> 4;
-    const int ntiles = KK * co_tiles * ci_tiles;
+    const int rowlen = 16 * KK, pitch = rowlen + 1;
+    int co_t = 16;
+    while (co_t * pitch > FIN_SMEM_FLOATS) co_t >>= 1;                   // 5x5: 4 output channels per tile
+    const int co_tiles = (cout + co_t - 1) / co_t, ci_tiles = cin >> 4;
     const float4 *g4 = reinterpret_cast<const float4 *>(gacc);
-    for (int tl = blockIdx.x; tl < ntiles; tl += gridDim.x) {
-        const int cit = tl % ci_tiles, cot = (tl / ci_tiles) % co_tiles, t = tl / (ci_tiles * co_tiles);
-        {
-            const int col = threadIdx.x & 63, co = cot * 64 + col, c4l = threadIdx.x >> 6, c4 = cit * 4 + c4l;
+    for (int tl = blockIdx.x; tl < co_tiles * ci_tiles; tl += gridDim.x) {
+        const int cit = tl % ci_tiles, cot = tl / ci_tiles;
+        // load: co fastest (coalesced 16-byte reads), then the 4 input-channel quads of the tile, then the taps
+        for (int e = threadIdx.x; e < co_t * 4 * KK; e += blockDim.x) {
+            const int col = e % co_t, c4l = (e / co_t) & 3, t = e / (co_t * 4);
+            const int co = cot * co_t + col;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (co < cout) v = __ldg(g4 + ((size_t)t * cin4 + c4) * cout + co);
-            float *tr = &tile[col][c4l * 4];
-            tr[0] = v.x; tr[1] = v.y; tr[2] = v.z; tr[3] = v.w;
+            if (co < cout) v = __ldg(g4 + ((size_t)t * cin4 + cit * 4 + c4l) * cout + co);
+            float *tr = tile + col * pitch + (c4l * 4) * KK + t;
+            tr[0] = v.x; tr[KK] = v.y; tr[2 * KK] = v.z; tr[3 * KK] = v.w;
         }
         __syncthreads();
-        {
-            const int cil = threadIdx.x & 15, ci = cit * 16 + cil;
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int col = (threadIdx.x >> 4) + 16 * r, co = cot * 64 + col;
-                if (co < cout && ci < cin_true) gW[((size_t)co * cin_true + ci) * KK + t] += tile[col][cil];
-            }
+        // store: for one output channel the tile's 16 * KK elements are contiguous in gW
+        const int kmax = min(rowlen, (cin_true - cit * 16) * KK);         // the padded input channels of the first layer do not exist in gW
+        for (int e = threadIdx.x; e < co_t * rowlen; e += blockDim.x) {
+            const int col = e / rowlen, k = e - col * rowlen;
+            const int co = cot * co_t + col;
+            if (co < cout && k < kmax) gW[((size_t)co * cin_true + cit * 16) * KK + k] += tile[col * pitch + k];
         }
         __syncthreads();
     }
     // ga[c][p] += gab[(rho(p) - first)/4][c][..] ; gb[c] += sum_p of the same (nn.Add gradBias, conv gradBias)
     if (fl.gab) {
-        float *red = &tile[0][0];
+        float *red = tile;
         for (int c = blockIdx.x; c < cout; c += gridDim.x) {
             float s = 0.f;
             for (int pt = threadIdx.x; pt < DG_POINTS; pt += blockDim.x) {
@@ -780,6 +795,7 @@ __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const FinalizeLayer
             __syncthreads();
         }
     }
+    DG_TL_OUT(tl, DG_TL_FINALIZE);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -837,6 +853,7 @@ struct HeadParams {
     int32_t *argmax;
     bf16 *dz_out;            // dZ_{L-1}: [n][C/8][R_out][8] (NULL: forward only)
     long long *dbg;          // optional phase timestamps (DG_TIMELINE=1)
+    unsigned long long *tl;  // optional step timeline (DG_TL=1)
     float *part;             // per-position partial gradients [n][9*C + 361]: weight-gradient partials, then dz of the 1-channel map
                              // (summed over positions by head_grad_reduce_kernel: no same-address atomics from 128 CTAs)
     int n, C, R;
@@ -881,9 +898,11 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     float *gws = ws + 9 * p.C;                                                         // [9][C] partial weight gradient
 
     dg_pdl_launch_dependents();
+    DG_TL_IN(p.tl, DG_TL_HEAD);
     if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
     __syncthreads();
     dg_pdl_wait();
+    DG_TL_GO(p.tl, DG_TL_HEAD);
     if (tid == 0) {
         mbar_arrive_expect_tx(&bar, img_bytes);
         const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
@@ -947,7 +966,7 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     const int tgt = p.targets ? p.targets[pos] : -1;
     if (valid && pt == tgt && p.loss_n) p.loss_n[pos] = -lp;
     HSTAMP(3);
-    if (!p.dz_out) return;
+    if (!p.dz_out) { DG_TL_OUT(p.tl, DG_TL_HEAD); return; }
 
     // ---- backward of LogSoftMax + NLL + ReLU on the 1-channel map
     float dzv = 0.f;
@@ -1029,6 +1048,7 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
         }
     }
     HSTAMP(5);
+    DG_TL_OUT(p.tl, DG_TL_HEAD);
 }
 
 // gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order.
@@ -1187,52 +1207,127 @@ struct SgdPackLayer {
     bf16 *wf, *wd;
     bf16 *ab;
     int cin_true, cin, cout, ksize;
+    // fused step: gradients straight from the weight-gradient kernel's accumulation buffers (NULL: read gW / gb / ga)
+    const float *gacc;           // [tap][cin/4][cout][4]
+    const float *gab;            // [(row - first)/4][cout][4]
+    int g_pitch, g_pad, g_first; // geometry of the layer's dZ image
 };
 
 __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__restrict__ table, float rate, const float *__restrict__ rate_dev,
-                                                       int R_out, int pitch_out, int pad_out, int smem_row) {
+                                                       int R_out, int pitch_out, int pad_out, int smem_row, unsigned long long *tl) {
     extern __shared__ float wrow[];                 // [8][smem_row]: the 8 updated weight rows
-    __shared__ float bnew[8];
+    __shared__ float bnew[8], bsum[8];
     dg_pdl_launch_dependents();
+    DG_TL_IN(tl, DG_TL_SGD);
     dg_pdl_wait();
+    DG_TL_GO(tl, DG_TL_SGD);
     const SgdPackLayer L = table[blockIdx.y];
     const float neg_rate = -(rate_dev ? *rate_dev : rate);
     const int KK = L.ksize * L.ksize, row = L.cin_true * KK;
     const int co0 = blockIdx.x * 8;
-    if (co0 >= L.cout) return;
+    if (co0 >= L.cout) { DG_TL_OUT(tl, DG_TL_SGD); return; }
     const int nco = min(8, L.cout - co0);
-    // ---- weights: update in place, keep the new values in shared memory
-    // the 8 rows are contiguous in the master vector: a flat, coalesced, unrolled sweep (few threads: keep loads in flight)
-    {
-        float *Wp = L.W + (size_t)co0 * row;
-        const float *Gp = L.gW + (size_t)co0 * row;
-        const int total = nco * row;
-#pragma unroll 4
-        for (int i = threadIdx.x; i < total; i += blockDim.x) {
-            const float v = fmaf(neg_rate, __ldg(Gp + i), Wp[i]);
-            Wp[i] = v;
-            if (L.wf) { const int r = i / row; wrow[r * smem_row + (i - r * row)] = v; }
+    const bool from_acc = L.gacc != nullptr;
+    if (threadIdx.x < 8) bsum[threadIdx.x] = 0.f;
+    if (from_acc) {
+        // the accumulation buffer [tap][cin/4][cout][4] is read in ITS order (8 output channels x 16 bytes = one 128-byte line) and
+        // transposed through shared memory into the rows the sweep below walks
+        const int cin4 = L.cin >> 2;
+        const float4 *g4 = reinterpret_cast<const float4 *>(L.gacc);
+        for (int e = threadIdx.x; e < KK * cin4 * 8; e += blockDim.x) {
+            const int r = e & 7, c4 = (e >> 3) % cin4, t = e / (8 * cin4);
+            if (r < nco) {
+                const float4 g = __ldg(g4 + ((size_t)t * cin4 + c4) * L.cout + co0 + r);
+                const float gj[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (c4 * 4 + j < L.cin_true) wrow[r * smem_row + (c4 * 4 + j) * KK + t] = gj[j];
+            }
+        }
+        __syncthreads();
+    }
+    // ---- weights: update in place, keep the new values in shared memory.  The 8 rows are contiguous in the master vector: a flat,
+    // coalesced sweep; the block is latency-bound, so every thread first issues all its loads (weights, gradients, and the
+    // per-point bias of the next phase) and only then computes
+    float *Wp = L.W + (size_t)co0 * row;
+    const float *Gp = L.gW + (size_t)co0 * row;
+    const int total = nco * row;
+    float av[3], ag[3];                             // per-point bias: nco * 361 <= 2888 elements, up to 3 per thread
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int i = threadIdx.x + k * 1024;
+        av[k] = ag[k] = 0.f;
+        if (i < nco * DG_POINTS) {
+            const size_t gi = (size_t)co0 * DG_POINTS + i;
+            av[k] = L.a[gi];
+            if (from_acc) {
+                const int r = i / DG_POINTS, pt = i - r * DG_POINTS;
+                const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
+                const int rr = (x + L.g_pad) * L.g_pitch + y + L.g_pad - L.g_first;
+                ag[k] = __ldg(L.gab + ((size_t)(rr >> 2) * L.cout + co0 + r) * 4 + (rr & 3));
+            } else {
+                ag[k] = __ldg(L.ga + gi);
+            }
+        }
+        if (from_acc) {
+            // conv gradBias = sum over the points of nn.Add's gradBias.  A warp spans at most two channels (361 > 32): two shuffle
+            // reductions, then one shared-memory add per channel and warp (1024 threads adding to 8 words directly serialise)
+            const int r_lo = (int)((threadIdx.x & ~31u) + k * 1024) / DG_POINTS;
+            const int r_me = i / DG_POINTS;
+            float s_lo = (i < nco * DG_POINTS && r_me == r_lo) ? ag[k] : 0.f, s_hi = (i < nco * DG_POINTS && r_me != r_lo) ? ag[k] : 0.f;
+#pragma unroll
+            for (int sh = 16; sh > 0; sh >>= 1) { s_lo += __shfl_xor_sync(0xffffffffu, s_lo, sh); s_hi += __shfl_xor_sync(0xffffffffu, s_hi, sh); }
+            if ((threadIdx.x & 31) == 0) {
+                if (r_lo < nco) atomicAdd(&bsum[r_lo], s_lo);
+                if (r_lo + 1 < nco) atomicAdd(&bsum[r_lo + 1], s_hi);
+            }
         }
     }
+    for (int base = threadIdx.x; base < total; base += 12 * 1024) {
+        float wv[12], gv[12];
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+            const int i = base + k * 1024;
+            wv[k] = gv[k] = 0.f;
+            if (i < total) {
+                wv[k] = Wp[i];
+                if (from_acc) { const int r = i / row; gv[k] = wrow[r * smem_row + (i - r * row)]; }
+                else gv[k] = __ldg(Gp + i);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 12; ++k) {
+            const int i = base + k * 1024;
+            if (i < total) {
+                const float v = fmaf(neg_rate, gv[k], wv[k]);
+                Wp[i] = v;
+                if (L.wf) { const int r = i / row; wrow[r * smem_row + (i - r * row)] = v; }
+            }
+        }
+    }
+    if (from_acc) __syncthreads();                  // bsum complete
     if (threadIdx.x < nco) {
-        const float v = fmaf(neg_rate, L.gb[co0 + threadIdx.x], L.b[co0 + threadIdx.x]);
+        const float v = fmaf(neg_rate, from_acc ? bsum[threadIdx.x] : L.gb[co0 + threadIdx.x], L.b[co0 + threadIdx.x]);
         L.b[co0 + threadIdx.x] = v;
         bnew[threadIdx.x] = v;
     }
     __syncthreads();
     // ---- per-point bias: update, and emit b + a in the blocked epilogue layout (32 contiguous bytes per point)
-    for (int i = threadIdx.x; i < nco * DG_POINTS; i += blockDim.x) {
-        const int r = i / DG_POINTS, pt = i - r * DG_POINTS;
-        const size_t gi = (size_t)(co0 + r) * DG_POINTS + pt;
-        const float v = fmaf(neg_rate, L.ga[gi], L.a[gi]);
-        L.a[gi] = v;
-        if (L.ab) {
-            const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
-            const int rho = (x + pad_out) * pitch_out + y + pad_out;
-            L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + r] = __float2bfloat16(v + bnew[r]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int i = threadIdx.x + k * 1024;
+        if (i < nco * DG_POINTS) {
+            const int r = i / DG_POINTS, pt = i - r * DG_POINTS;
+            const float v = fmaf(neg_rate, ag[k], av[k]);
+            L.a[(size_t)co0 * DG_POINTS + i] = v;
+            if (L.ab) {
+                const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
+                const int rho = (x + pad_out) * pitch_out + y + pad_out;
+                L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + r] = __float2bfloat16(v + bnew[r]);
+            }
         }
     }
-    if (!L.wf) return;
+    if (!L.wf) { DG_TL_OUT(tl, DG_TL_SGD); return; }
     // ---- forward operand wf[t][ci/8][co][8]: one thread per (t, ci8, r) writes 8 ci = 16 bytes; r fastest -> 128-byte runs
     const int cin8 = L.cin >> 3;
     for (int i = threadIdx.x; i < KK * cin8 * 8; i += blockDim.x) {
@@ -1256,6 +1351,7 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
             *reinterpret_cast<uint4 *>(L.wd + (((size_t)t * (L.cout >> 3) + (co0 >> 3)) * L.cin + ci) * 8) = *reinterpret_cast<const uint4 *>(v);
         }
     }
+    DG_TL_OUT(tl, DG_TL_SGD);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1278,6 +1374,10 @@ struct Bf16Path {
     PackLayer *pack_table = nullptr;       // device copy, one entry per conv layer
     FinalizeLayer *fin_table = nullptr;    // device copy, one entry per conv layer
     SgdPackLayer *sgd_table = nullptr;     // device copy, one entry per layer (the 1-channel last layer included)
+    SgdPackLayer *sgd_table_acc = nullptr; // same, conv layers reading the accumulation buffers (fused step)
+    std::vector<SgdPackLayer> sgd_host;
+    bool defer_grads = false;              // fused steps hand the conv gradients to the SGD kernel in the accumulation buffers
+    bool grads_pending = false;            // the conv layers' gradient of the last fused step is still in gacc / gab, not in m->grads
     int sgd_smem_row = 0, sgd_max_co8 = 0;
     std::vector<FinalizeLayer> fin_host;
     float *gacc = nullptr;                 // weight-gradient accumulation buffers of all conv layers (default path)
@@ -1291,7 +1391,7 @@ struct Bf16Path {
     // the small HBM-bound gradient kernels (bias gradients, split-K reduction) run on a side stream, under the
     // tensor-core kernels of the main stream
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_dz = nullptr, ev_wgrad = nullptr, ev_bias[2] = {nullptr, nullptr}, ev_reduce[2] = {nullptr, nullptr}, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_memset = nullptr, ev_dz = nullptr, ev_wgrad = nullptr, ev_bias[2] = {nullptr, nullptr}, ev_reduce[2] = {nullptr, nullptr}, ev_join = nullptr;
     int num_sms = 148;
     bool head_bwd_done = false;
 };
@@ -1314,6 +1414,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     static const bool timeline = getenv("DG_TIMELINE") != nullptr;
     if (timeline && !dbg) cudaMalloc(&dbg, (148 * 10 + 64) * sizeof(long long));
     cp.dbg = timeline ? dbg : nullptr;
+    cp.tl = c->tl; cp.tl_id = cp.mode ? DG_TL_DGRAD : (cp.ksize == 5 || cp.cin < cp.cout ? DG_TL_CONV0 : DG_TL_CONV);
     const size_t img_bytes = ((size_t)(cp.cin / 8) * cp.R_in * 16 + 1023) & ~(size_t)1023;
     // CTA pairs (cta_group::2) when the layer is one N block and one K panel: each CTA keeps half of every weight stage
     // (opt-in, DG_PAIR=1: measured slower at batch 128 -- the two SMs of a TPC then drain their accumulators in lock-step and
@@ -1455,10 +1556,13 @@ int dg_bf16_create(dg_model *m) {
             sg[l].gW = m->grads + li.offW; sg[l].gb = m->grads + li.offB; sg[l].ga = m->grads + li.offA;
             sg[l].wf = l < L - 1 ? b->ops[l].wf : nullptr; sg[l].wd = l < L - 1 ? b->ops[l].wd : nullptr; sg[l].ab = l < L - 1 ? b->ops[l].ab : nullptr;
             sg[l].cin_true = li.cin; sg[l].cin = l < L - 1 ? b->ops[l].cin_pad : li.cin; sg[l].cout = li.cout; sg[l].ksize = li.k;
+            sg[l].gacc = nullptr; sg[l].gab = nullptr; sg[l].g_pitch = sg[l].g_pad = sg[l].g_first = 0;
             b->sgd_smem_row = std::max(b->sgd_smem_row, li.cin * li.k * li.k + 1);
             b->sgd_max_co8 = std::max(b->sgd_max_co8, (li.cout + 7) / 8);
         }
+        b->sgd_host = sg;
         DG_CUDA(cudaMalloc((void **)&b->sgd_table, sg.size() * sizeof(SgdPackLayer)));
+        DG_CUDA(cudaMalloc((void **)&b->sgd_table_acc, sg.size() * sizeof(SgdPackLayer)));
         DG_CUDA(cudaMemcpyAsync(b->sgd_table, sg.data(), sg.size() * sizeof(SgdPackLayer), cudaMemcpyHostToDevice, st));
         DG_CUDA(cudaFuncSetAttribute(sgd_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * b->sgd_smem_row * 4));
         DG_CUDA(cudaMalloc((void **)&b->fin_table, ft.size() * sizeof(FinalizeLayer)));
@@ -1481,12 +1585,22 @@ int dg_bf16_create(dg_model *m) {
     }
     DG_CUDA(cudaMalloc((void **)&b->gacc, b->gacc_floats * 4));
     for (int l = 0; l < L - 1; ++l) { b->fin_host[l].gacc = b->gacc + b->gacc_off[l]; b->fin_host[l].gab = b->fused_bias ? b->gacc + b->gab_off[l] : nullptr; }
+    b->defer_grads = b->fused_bias && getenv("DG_NO_DEFER") == nullptr;
+    if (b->fused_bias) {
+        std::vector<SgdPackLayer> sa = b->sgd_host;
+        for (int l = 0; l < L - 1; ++l) {
+            const Geom &gl = l == 0 ? b->g_first : b->g3;
+            sa[l].gacc = b->gacc + b->gacc_off[l]; sa[l].gab = b->gacc + b->gab_off[l];
+            sa[l].g_pitch = gl.pitch; sa[l].g_pad = gl.pad; sa[l].g_first = gl.first;
+        }
+        DG_CUDA(cudaMemcpyAsync(b->sgd_table_acc, sa.data(), sa.size() * sizeof(SgdPackLayer), cudaMemcpyHostToDevice, st));
+    }
     DG_CUDA(cudaMemcpyAsync(b->fin_table, b->fin_host.data(), b->fin_host.size() * sizeof(FinalizeLayer), cudaMemcpyHostToDevice, st));
     DG_CUDA(cudaStreamSynchronize(st));
     DG_CUDA(cudaMalloc((void **)&b->scratch, 2 * scratch));
     b->scratch_bytes = scratch;
     DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
-    cudaEvent_t *evs[] = {&b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
+    cudaEvent_t *evs[] = {&b->ev_fork, &b->ev_memset, &b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
     for (cudaEvent_t *e : evs) DG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
@@ -1509,6 +1623,7 @@ void dg_bf16_destroy(dg_model *m) {
     cudaFree(b->pack_table);
     cudaFree(b->fin_table);
     cudaFree(b->sgd_table);
+    cudaFree(b->sgd_table_acc);
     cudaFree(b->head_part);
     if (b->side) cudaStreamDestroy(b->side);
     delete b;
@@ -1533,13 +1648,34 @@ int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev) {
     dg_ctx *c = m->ctx;
     {
         dg_prof_scope _ps(c, DG_K_SGD);
+        static const bool sgd_plain = getenv("DG_SGD_NO_PDL") != nullptr;
+        if (sgd_plain) sgd_pack_kernel<<<dim3(b->sgd_max_co8, m->L), dim3(1024), (size_t)8 * b->sgd_smem_row * 4, c->stream>>>((const SgdPackLayer *)(b->grads_pending ? b->sgd_table_acc : b->sgd_table), rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row, c->tl);
+        else
         DG_CUDA(dg_launch_pdl(sgd_pack_kernel, dim3(b->sgd_max_co8, m->L), dim3(1024), (size_t)8 * b->sgd_smem_row * 4, c->stream,
-                              (const SgdPackLayer *)b->sgd_table, rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row));
+                              (const SgdPackLayer *)(b->grads_pending ? b->sgd_table_acc : b->sgd_table), rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row, c->tl));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
 }
+
+// materialise the conv layers' gradient of the last fused step in the Torch7-order vector (no-op when it already is there)
+int dg_bf16_sync_grads(dg_model *m) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    if (!b->grads_pending) return 0;
+    const LayerInfo &l0 = m->layers[0], &lh = m->layers[m->L - 1];
+    DG_CUDA(cudaMemsetAsync(m->grads + l0.offW, 0, (lh.offW - l0.offW) * 4, c->stream));
+    wgrad_finalize_kernel<<<dim3(96, m->L - 1), 256, FIN_SMEM_FLOATS * 4, c->stream>>>(b->fin_table, nullptr);
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    b->grads_pending = false;
+    return 0;
+}
+void dg_bf16_drop_pending_grads(dg_model *m) { m->bf->grads_pending = false; }
+// a replayed step graph runs no host code of dg_bf16_backward: restore what the captured step leaves behind
+void dg_bf16_after_fused_step(dg_model *m) { m->bf->grads_pending = m->bf->defer_grads; }
+bool dg_bf16_defers_grads(const dg_model *m) { return m->bf->defer_grads; }
 
 int dg_bf16_stage_raw(dg_model *m) {
     Bf16Path *b = m->bf;
@@ -1581,6 +1717,7 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     static const bool htl = getenv("DG_TIMELINE") != nullptr;
     if (htl && !hdbg) cudaMalloc(&hdbg, 4096 * 8 * sizeof(long long));
     hp.dbg = htl && m->n <= 4096 ? hdbg : nullptr;
+    hp.tl = c->tl;
     hp.n = m->n; hp.C = m->C; hp.R = DG_R3;
     hp.R_out = go.rows; hp.pitch_out = go.pitch; hp.pad_out = go.pad;
     hp.scale = scale;
@@ -1641,7 +1778,14 @@ int dg_bf16_forward(dg_model *m) {
 int dg_bf16_backward(dg_model *m, float scale) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
-    if (!b->deterministic) DG_CUDA(cudaMemsetAsync(b->gacc, 0, b->gacc_floats * 4, c->stream));
+    // the accumulation buffers are cleared on the side stream while the head and the input-gradient chain run (a memset node between
+    // two kernels of the main stream costs its 5 us and the programmatic launch overlap of its neighbours)
+    if (!b->deterministic) {
+        DG_CUDA(cudaEventRecord(b->ev_fork, c->stream));
+        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_fork, 0));
+        DG_CUDA(cudaMemsetAsync(b->gacc, 0, b->gacc_floats * 4, b->side));
+        DG_CUDA(cudaEventRecord(b->ev_memset, b->side));
+    }
     if (int rc = launch_head(m, true, scale)) return rc;      // its per-position gradient partials are summed on the side stream
     // ---- input gradients first: dZ_{l} -> dZ_{l-1} for conv layers l = L-2 .. 1 (transposed conv with flipped taps, masked by
     // the ReLU of layer l's input h_l); with C <= 128 the whole chain is one kernel with dZ resident in shared memory
@@ -1670,14 +1814,17 @@ int dg_bf16_backward(dg_model *m, float scale) {
     // every dZ_l is complete on the main stream: the side stream may read them
     DG_CUDA(cudaEventRecord(b->ev_dz, c->stream));
     DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
+    if (!b->deterministic) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_memset, 0));     // the weight-gradient kernels add into the cleared buffers
     bool rec_reduce[2] = {false, false};   // events recorded in THIS pass (stream capture forbids waiting on older records)
     static long long *wdbg = nullptr;
     static const bool wtl = getenv("DG_TIMELINE") != nullptr;
     if (wtl && !wdbg) cudaMalloc(&wdbg, 148 * 8 * sizeof(long long));
     {
         const LayerInfo &lh = m->layers[m->L - 1];
-        dg_prof_scope _ps(c, DG_K_HEAD, b->side);
-        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, b->side>>>(b->head_part, m->n, m->C, m->grads + lh.offW,
+        static const bool hgr_main = getenv("DG_HGR_MAIN") != nullptr;
+        cudaStream_t hst = hgr_main ? c->stream : b->side;
+        dg_prof_scope _ps(c, DG_K_HEAD, hst);
+        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, hst>>>(b->head_part, m->n, m->C, m->grads + lh.offW,
                                                                                        m->grads + lh.offB, m->grads + lh.offA);
         c->launches++;
     }
@@ -1719,6 +1866,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         wp.ngroups = ngroups;
         wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits / ngroups; wp.nstages = w.nstages;
         wp.dbg = wtl ? wdbg : nullptr;
+        wp.tl = c->tl; wp.tl_id = l == 0 ? DG_TL_WGRAD0 : DG_TL_WGRAD;
         // deterministic path: this scratch half was last read by the reduction two layers ago
         if (b->deterministic && rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
         { dg_prof_scope _ps(c, DG_K_WGRAD);
@@ -1738,30 +1886,41 @@ int dg_bf16_backward(dg_model *m, float scale) {
         for (int j = 0; j < nl; ++j) {
             const int lj = l - j;
             const LayerInfo &lij = m->layers[lj];
-            { dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
-            if (b->deterministic)
+            if (b->deterministic) {
+                dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
                 wgrad_reduce_kernel<<<b->num_sms * 8, 256, 0, b->side>>>(scratch, m->grads + lij.offW, lij.cin, b->ops[lj].cin_pad, lij.cout, lij.k, w.nb,
                                                                          w.n_mblk, w.n_nblk, w.splits);
+                c->launches++;
             }
-            if (b->deterministic) c->launches++;
         }
         DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
         rec_reduce[par] = true;
         l -= nl;
     }
-    if (!b->deterministic) {
+    // Inside dg_train_step the SGD kernel reads the accumulation buffers itself: the Torch7-order gradient vector is not
+    // materialised (dg_bf16_sync_grads does it on demand, e.g. for dg_model_get_grads)
+    const bool defer = m->fused_step && b->defer_grads;
+    b->grads_pending = defer;
+    if (!b->deterministic && !defer) {
         // one launch folds every layer's accumulation buffer into the Torch7-order gradient
         dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
-        wgrad_finalize_kernel<<<dim3(48, m->L - 1), 256, 0, b->side>>>(b->fin_table);
+        wgrad_finalize_kernel<<<dim3(96, m->L - 1), 256, FIN_SMEM_FLOATS * 4, b->side>>>(b->fin_table, c->tl);
         c->launches++;
     }
     DG_CUDA(cudaEventRecord(b->ev_join, b->side));
     DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_join, 0));
     // data parallel: all weight gradients of the 3x3 layers become final together (one persistent launch), so the exchange
-    // is ONE allreduce of the whole flat gradient vector -- latency-optimal for 8.4 MB over NVLink
+    // is ONE allreduce of the whole gradient -- latency-optimal for 8.4 MB over NVLink (plus the 6 KB of the head layer when the
+    // conv layers' gradient stays in the accumulation buffers)
     if (m->fused_step && c->world > 1) {
         const LayerInfo &l0 = m->layers[0], &lh = m->layers[m->L - 1];
-        if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS - l0.offW)) return rc;
+        const size_t head_n = lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS;
+        if (defer) {
+            if (int rc = dg_dp_bucket(c, b->gacc, b->gacc_floats)) return rc;
+            if (int rc = dg_dp_bucket(c, m->grads + lh.offW, head_n)) return rc;
+        } else {
+            if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + head_n - l0.offW)) return rc;
+        }
     }
     DG_CUDA(cudaGetLastError());
     return 0;

@@ -59,6 +59,11 @@ int dg_ctx_flush_l2(dg_ctx *ctx);
 int dg_prof_begin(dg_ctx *ctx);
 int dg_prof_end(dg_ctx *ctx);
 int dg_prof_get(dg_ctx *ctx, int kind, float *ms_total, long long *launches);
+/* Step timeline that also sees inside a replayed CUDA graph (process started with DG_TL=1): per kernel of the training step
+ * {first CTA in, first CTA past its dependency wait, last CTA out} in globaltimer nanoseconds, in the order first conv, conv
+ * chain, head, input-gradient chain, weight gradient (3x3 layers), weight gradient (first layer), gradient finalize, SGD, head
+ * reduction; copies min(n, 27) values, then resets the stamps.  Profiling aid, no reference counterpart. */
+int dg_prof_timeline(dg_ctx *ctx, unsigned long long *out, int n);
 
 /* ---- data parallel (nn.DataParallelTable(1), experiments.lua:155-168) ---------------------- */
 /* One process per GPU.  Rank 0 calls dg_dp_unique_id and ships the 128 bytes to the other ranks

@@ -16,3 +16,20 @@ for _ in range(steps):
     m.encode_resident()
     loss = m.train_step(0.01)
 print("loss", loss, "launches", ctx.launch_count())
+
+if os.environ.get("DG_TL"):
+    # in-graph timeline of the last step (globaltimer ns relative to the first kernel of the step)
+    from deepgo_b200 import ffi, lib
+    names = ["conv0", "conv chain", "head", "dgrad chain", "wgrad 3x3", "wgrad first", "finalize", "sgd", "head reduce"]
+    buf = ffi.new("unsigned long long[27]")
+    lib().dg_prof_timeline(ctx.h, buf, 27)          # drop the stamps of the steps so far
+    m.encode_resident()
+    m.train_step(0.01)
+    lib().dg_prof_timeline(ctx.h, buf, 27)
+    v = [int(buf[i]) for i in range(27)]
+    t0 = min(x for i, x in enumerate(v) if i % 3 == 0 and x != 2**64 - 1)
+    for k, nm in enumerate(names):
+        a, g, e = v[3 * k:3 * k + 3]
+        if a == 2**64 - 1:
+            continue
+        print("%-12s in %8.1f us  go %8.1f us  out %8.1f us   (%.1f us)" % (nm, (a - t0) / 1e3, (g - t0) / 1e3, (e - t0) / 1e3, (e - g) / 1e3))
