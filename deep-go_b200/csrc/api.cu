@@ -466,8 +466,7 @@ extern "C" int dg_sgd_step(dg_model *m, float rate) {
 // one fused step on the context's stream: eval() of train.lua:4-12 followed by SGD:step (train.lua:131)
 static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
     dg_ctx *c = m->ctx;
-    static const bool exp_fullmemset = getenv("DG_EXP_FULLMEMSET") != nullptr;
-    if (m->bf && dg_bf16_defers_grads(m) && !exp_fullmemset) {
+    if (m->bf && dg_bf16_defers_grads(m)) {
         // the conv layers' gradient goes from the accumulation buffers straight into the SGD kernel: only the head's slice is summed in place
         const LayerInfo &lh = m->layers[m->L - 1];
         DG_CUDA(cudaMemsetAsync(m->grads + lh.offW, 0, (m->P - lh.offW) * 4, c->stream));

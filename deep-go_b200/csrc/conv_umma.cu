@@ -1213,10 +1213,15 @@ struct SgdPackLayer {
     int g_pitch, g_pad, g_first; // geometry of the layer's dZ image
 };
 
-__global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__restrict__ table, float rate, const float *__restrict__ rate_dev,
+#ifndef SGD_CO_B
+#define SGD_CO_B 4
+#define SGD_NT 256
+#endif
+template <int CO_B, int NT>      // output channels per block, threads per block
+__global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__restrict__ table, float rate, const float *__restrict__ rate_dev,
                                                        int R_out, int pitch_out, int pad_out, int smem_row, unsigned long long *tl) {
-    extern __shared__ float wrow[];                 // [8][smem_row]: the 8 updated weight rows
-    __shared__ float bnew[8], bsum[8];
+    extern __shared__ float wrow[];                 // [CO_B][smem_row]: the block's updated weight rows
+    __shared__ float bnew[CO_B], bsum[CO_B];
     dg_pdl_launch_dependents();
     DG_TL_IN(tl, DG_TL_SGD);
     dg_pdl_wait();
@@ -1224,18 +1229,19 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
     const SgdPackLayer L = table[blockIdx.y];
     const float neg_rate = -(rate_dev ? *rate_dev : rate);
     const int KK = L.ksize * L.ksize, row = L.cin_true * KK;
-    const int co0 = blockIdx.x * 8;
+    const int co0 = blockIdx.x * CO_B;
     if (co0 >= L.cout) { DG_TL_OUT(tl, DG_TL_SGD); return; }
-    const int nco = min(8, L.cout - co0);
+    const int nco = min(CO_B, L.cout - co0);
+    constexpr int NB = (CO_B * DG_POINTS + NT - 1) / NT;      // per-point bias elements per thread
     const bool from_acc = L.gacc != nullptr;
-    if (threadIdx.x < 8) bsum[threadIdx.x] = 0.f;
+    if (threadIdx.x < CO_B) bsum[threadIdx.x] = 0.f;
     if (from_acc) {
         // the accumulation buffer [tap][cin/4][cout][4] is read in ITS order (8 output channels x 16 bytes = one 128-byte line) and
         // transposed through shared memory into the rows the sweep below walks
         const int cin4 = L.cin >> 2;
         const float4 *g4 = reinterpret_cast<const float4 *>(L.gacc);
-        for (int e = threadIdx.x; e < KK * cin4 * 8; e += blockDim.x) {
-            const int r = e & 7, c4 = (e >> 3) % cin4, t = e / (8 * cin4);
+        for (int e = threadIdx.x; e < KK * cin4 * CO_B; e += NT) {
+            const int r = e % CO_B, c4 = (e / CO_B) % cin4, t = e / (CO_B * cin4);
             if (r < nco) {
                 const float4 g = __ldg(g4 + ((size_t)t * cin4 + c4) * L.cout + co0 + r);
                 const float gj[4] = {g.x, g.y, g.z, g.w};
@@ -1252,10 +1258,10 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
     float *Wp = L.W + (size_t)co0 * row;
     const float *Gp = L.gW + (size_t)co0 * row;
     const int total = nco * row;
-    float av[3], ag[3];                             // per-point bias: nco * 361 <= 2888 elements, up to 3 per thread
+    float av[NB], ag[NB];                           // per-point bias: nco * 361 elements
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int i = threadIdx.x + k * 1024;
+    for (int k = 0; k < NB; ++k) {
+        const int i = threadIdx.x + k * NT;
         av[k] = ag[k] = 0.f;
         if (i < nco * DG_POINTS) {
             const size_t gi = (size_t)co0 * DG_POINTS + i;
@@ -1271,8 +1277,8 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
         }
         if (from_acc) {
             // conv gradBias = sum over the points of nn.Add's gradBias.  A warp spans at most two channels (361 > 32): two shuffle
-            // reductions, then one shared-memory add per channel and warp (1024 threads adding to 8 words directly serialise)
-            const int r_lo = (int)((threadIdx.x & ~31u) + k * 1024) / DG_POINTS;
+            // reductions, then one shared-memory add per channel and warp (every thread adding to a handful of words directly serialises)
+            const int r_lo = (int)((threadIdx.x & ~31u) + k * NT) / DG_POINTS;
             const int r_me = i / DG_POINTS;
             float s_lo = (i < nco * DG_POINTS && r_me == r_lo) ? ag[k] : 0.f, s_hi = (i < nco * DG_POINTS && r_me != r_lo) ? ag[k] : 0.f;
 #pragma unroll
@@ -1283,11 +1289,11 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
             }
         }
     }
-    for (int base = threadIdx.x; base < total; base += 12 * 1024) {
+    for (int base = threadIdx.x; base < total; base += 12 * NT) {
         float wv[12], gv[12];
 #pragma unroll
         for (int k = 0; k < 12; ++k) {
-            const int i = base + k * 1024;
+            const int i = base + k * NT;
             wv[k] = gv[k] = 0.f;
             if (i < total) {
                 wv[k] = Wp[i];
@@ -1297,7 +1303,7 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
         }
 #pragma unroll
         for (int k = 0; k < 12; ++k) {
-            const int i = base + k * 1024;
+            const int i = base + k * NT;
             if (i < total) {
                 const float v = fmaf(neg_rate, gv[k], wv[k]);
                 Wp[i] = v;
@@ -1314,8 +1320,8 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
     __syncthreads();
     // ---- per-point bias: update, and emit b + a in the blocked epilogue layout (32 contiguous bytes per point)
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int i = threadIdx.x + k * 1024;
+    for (int k = 0; k < NB; ++k) {
+        const int i = threadIdx.x + k * NT;
         if (i < nco * DG_POINTS) {
             const int r = i / DG_POINTS, pt = i - r * DG_POINTS;
             const float v = fmaf(neg_rate, ag[k], av[k]);
@@ -1323,15 +1329,15 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
             if (L.ab) {
                 const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
                 const int rho = (x + pad_out) * pitch_out + y + pad_out;
-                L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + r] = __float2bfloat16(v + bnew[r]);
+                L.ab[((size_t)(co0 >> 3) * R_out + rho) * 8 + (co0 & 7) + r] = __float2bfloat16(v + bnew[r]);
             }
         }
     }
     if (!L.wf) { DG_TL_OUT(tl, DG_TL_SGD); return; }
-    // ---- forward operand wf[t][ci/8][co][8]: one thread per (t, ci8, r) writes 8 ci = 16 bytes; r fastest -> 128-byte runs
+    // ---- forward operand wf[t][ci/8][co][8]: one thread per (t, ci8, r) writes 8 ci = 16 bytes; r fastest -> 16 * CO_B byte runs
     const int cin8 = L.cin >> 3;
-    for (int i = threadIdx.x; i < KK * cin8 * 8; i += blockDim.x) {
-        const int r = i & 7, c8 = (i >> 3) % cin8, t = i / (8 * cin8);
+    for (int i = threadIdx.x; i < KK * cin8 * CO_B; i += NT) {
+        const int r = i % CO_B, c8 = (i / CO_B) % cin8, t = i / (CO_B * cin8);
         if (r >= nco) continue;
         __align__(16) bf16 v[8];
 #pragma unroll
@@ -1341,14 +1347,16 @@ __global__ void __launch_bounds__(1024) sgd_pack_kernel(const SgdPackLayer *__re
         }
         *reinterpret_cast<uint4 *>(L.wf + (((size_t)t * cin8 + c8) * L.cout + co0 + r) * 8) = *reinterpret_cast<const uint4 *>(v);
     }
-    // ---- input-gradient operand wd[t'][co/8][ci][8] = W[co][ci][KK-1-t']: one thread per (t', ci) writes the 8 co of this block
-    if (L.wd && nco == 8) {
-        for (int i = threadIdx.x; i < KK * L.cin; i += blockDim.x) {
+    // ---- input-gradient operand wd[t'][co/8][ci][8] = W[co][ci][KK-1-t']: one thread per (t', ci) writes the CO_B co of this block
+    if (L.wd && nco == CO_B) {
+        for (int i = threadIdx.x; i < KK * L.cin; i += NT) {
             const int ci = i % L.cin, t = i / L.cin;
-            __align__(16) bf16 v[8];
+            __align__(16) bf16 v[CO_B];
 #pragma unroll
-            for (int r = 0; r < 8; ++r) v[r] = __float2bfloat16(ci < L.cin_true ? wrow[r * smem_row + ci * KK + (KK - 1 - t)] : 0.f);
-            *reinterpret_cast<uint4 *>(L.wd + (((size_t)t * (L.cout >> 3) + (co0 >> 3)) * L.cin + ci) * 8) = *reinterpret_cast<const uint4 *>(v);
+            for (int r = 0; r < CO_B; ++r) v[r] = __float2bfloat16(ci < L.cin_true ? wrow[r * smem_row + ci * KK + (KK - 1 - t)] : 0.f);
+            bf16 *dst = L.wd + (((size_t)t * (L.cout >> 3) + (co0 >> 3)) * L.cin + ci) * 8 + (co0 & 7);
+            if (CO_B == 8) *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(v);
+            else *reinterpret_cast<uint2 *>(dst) = *reinterpret_cast<const uint2 *>(v);
         }
     }
     DG_TL_OUT(tl, DG_TL_SGD);
@@ -1558,13 +1566,13 @@ int dg_bf16_create(dg_model *m) {
             sg[l].cin_true = li.cin; sg[l].cin = l < L - 1 ? b->ops[l].cin_pad : li.cin; sg[l].cout = li.cout; sg[l].ksize = li.k;
             sg[l].gacc = nullptr; sg[l].gab = nullptr; sg[l].g_pitch = sg[l].g_pad = sg[l].g_first = 0;
             b->sgd_smem_row = std::max(b->sgd_smem_row, li.cin * li.k * li.k + 1);
-            b->sgd_max_co8 = std::max(b->sgd_max_co8, (li.cout + 7) / 8);
+            b->sgd_max_co8 = std::max(b->sgd_max_co8, (li.cout + SGD_CO_B - 1) / SGD_CO_B);
         }
         b->sgd_host = sg;
         DG_CUDA(cudaMalloc((void **)&b->sgd_table, sg.size() * sizeof(SgdPackLayer)));
         DG_CUDA(cudaMalloc((void **)&b->sgd_table_acc, sg.size() * sizeof(SgdPackLayer)));
         DG_CUDA(cudaMemcpyAsync(b->sgd_table, sg.data(), sg.size() * sizeof(SgdPackLayer), cudaMemcpyHostToDevice, st));
-        DG_CUDA(cudaFuncSetAttribute(sgd_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * b->sgd_smem_row * 4));
+        DG_CUDA(cudaFuncSetAttribute(sgd_pack_kernel<SGD_CO_B, SGD_NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SGD_CO_B * b->sgd_smem_row * 4));
         DG_CUDA(cudaMalloc((void **)&b->fin_table, ft.size() * sizeof(FinalizeLayer)));
         DG_CUDA(cudaMalloc((void **)&b->pack_table, tab.size() * sizeof(PackLayer)));
         DG_CUDA(cudaMemcpyAsync(b->pack_table, tab.data(), tab.size() * sizeof(PackLayer), cudaMemcpyHostToDevice, st));
@@ -1648,10 +1656,7 @@ int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev) {
     dg_ctx *c = m->ctx;
     {
         dg_prof_scope _ps(c, DG_K_SGD);
-        static const bool sgd_plain = getenv("DG_SGD_NO_PDL") != nullptr;
-        if (sgd_plain) sgd_pack_kernel<<<dim3(b->sgd_max_co8, m->L), dim3(1024), (size_t)8 * b->sgd_smem_row * 4, c->stream>>>((const SgdPackLayer *)(b->grads_pending ? b->sgd_table_acc : b->sgd_table), rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row, c->tl);
-        else
-        DG_CUDA(dg_launch_pdl(sgd_pack_kernel, dim3(b->sgd_max_co8, m->L), dim3(1024), (size_t)8 * b->sgd_smem_row * 4, c->stream,
+        DG_CUDA(dg_launch_pdl(sgd_pack_kernel<SGD_CO_B, SGD_NT>, dim3(b->sgd_max_co8, m->L), dim3(SGD_NT), (size_t)SGD_CO_B * b->sgd_smem_row * 4, c->stream,
                               (const SgdPackLayer *)(b->grads_pending ? b->sgd_table_acc : b->sgd_table), rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row, c->tl));
     }
     c->launches++;
@@ -1821,8 +1826,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
     if (wtl && !wdbg) cudaMalloc(&wdbg, 148 * 8 * sizeof(long long));
     {
         const LayerInfo &lh = m->layers[m->L - 1];
-        static const bool hgr_main = getenv("DG_HGR_MAIN") != nullptr;
-        cudaStream_t hst = hgr_main ? c->stream : b->side;
+        cudaStream_t hst = b->side;
         dg_prof_scope _ps(c, DG_K_HEAD, hst);
         head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, hst>>>(b->head_part, m->n, m->C, m->grads + lh.offW,
                                                                                        m->grads + lh.offB, m->grads + lh.offA);
