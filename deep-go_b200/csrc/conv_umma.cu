@@ -1051,6 +1051,239 @@ __global__ void __launch_bounds__(384, 1) head_bf16_kernel(const HeadParams p) {
     DG_TL_OUT(p.tl, DG_TL_HEAD);
 }
 
+// ---------------------------------------------------------------------------------------------
+// head on the tensor cores (C <= 128): the same math as head_bf16_kernel, three small GEMMs instead of SIMT loops.
+//   logits   G[row][t] = sum_c in[row][c] * W[c][t]            (M = rows, K = C, N = 32), then z[rho] = sum_t G[rho + off(t)][t]
+//   gW       D[c][t]   = sum_row in[row][c] * dz[row - off(t)]  (M = C -> 128, K = 432 rows, N = 32)
+//   dZ_{L-1} [rho][c]  = sum_t dz[rho - off(t)] * W[c][t]       (M = rows, K = 32, N = C), then the ReLU mask of in
+// fp32 factors are split into bf16 hi + lo columns (hi*hi + lo*hi + hi*lo), so the results keep fp32-level accuracy.
+// The 32 "tap" columns j are: 0..8 hi(t), 9..17 lo(t), 18..26 hi(t) again (pairs with the lo weights), 27..31 zero.
+// ---------------------------------------------------------------------------------------------
+#define HU_ROWS DG_R3
+__global__ void __launch_bounds__(384, 1) head_umma_kernel(const HeadParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar_img, bar_mma;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ float red[12];
+    __shared__ int redi[12];
+    __shared__ float dzs[HU_ROWS + 64];          // dz of the 1-channel map by image row (+32), zero at pads and beyond
+    const int pos = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    HSTAMP(0);
+    const int chunks = p.C >> 3;
+    const uint32_t img_bytes = (uint32_t)chunks * HU_ROWS * 16;
+    // shared-memory map (the image region is sized for 16 chunks: the M = 128 weight-gradient MMA reads that far)
+    uint8_t *img = smem;                                         // [C/8][432][8] bf16
+    uint8_t *bw = smem + 16 * HU_ROWS * 16 + 2048;               // [C/8][32][8] bf16: W hi/lo columns, K-major B of the logits GEMM
+    uint8_t *b2 = bw + 16 * 32 * 16;                             // [4][128][8] bf16: W rows by tap column, K-major B of the dZ GEMM
+    uint8_t *dzim = b2 + 4 * 128 * 16;                           // [4][432][8] bf16: shifted dz columns (A of dZ, B of gW)
+    float *gs = reinterpret_cast<float *>(dzim + 4 * HU_ROWS * 16);   // [432][9] fp32: G
+
+    dg_pdl_launch_dependents();
+    DG_TL_IN(p.tl, DG_TL_HEAD);
+    if (tid == 0) { mbar_init(&bar_img, 1); mbar_init(&bar_mma, 1); fence_barrier_init(); }
+    if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
+    // weights are parameters (not produced by the previous kernel): pack them before the dependency wait
+    for (int i = tid; i < 32 * p.C; i += blockDim.x) {
+        const int c = i % p.C, j = i / p.C;                      // tap column j of channel c
+        const int t = j < 9 ? j : (j < 18 ? j - 9 : j - 18);
+        float hi = 0.f, lo = 0.f;
+        if (j < 27) {
+            const float w = p.W[c * 9 + t];
+            const bf16 h = __float2bfloat16(w);
+            hi = __bfloat162float(h);
+            lo = w - hi;
+        }
+        // logits B: columns 0..8 hi, 9..17 lo;  dZ B: rows 0..8 hi (x dz hi), 9..17 hi (x dz lo), 18..26 lo (x dz hi)
+        reinterpret_cast<bf16 *>(bw)[((size_t)(c >> 3) * 32 + j) * 8 + (c & 7)] = __float2bfloat16(j < 9 ? hi : (j < 18 ? lo : 0.f));
+        reinterpret_cast<bf16 *>(b2)[((size_t)(j >> 3) * 128 + c) * 8 + (j & 7)] = __float2bfloat16(j < 18 ? hi : (j < 27 ? lo : 0.f));
+    }
+    for (int i = tid; i < HU_ROWS + 64; i += blockDim.x) dzs[i] = 0.f;
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    dg_pdl_wait();
+    DG_TL_GO(p.tl, DG_TL_HEAD);
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&bar_img, img_bytes);
+        const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
+        for (int c = 0; c < chunks; ++c) bulk_g2s(img + (size_t)c * HU_ROWS * 16, src + (size_t)c * HU_ROWS * 16, (uint32_t)HU_ROWS * 16, &bar_img);
+    }
+    mbar_wait(&bar_img, 0);
+    HSTAMP(1);
+
+    // ---- G = in x W: 4 row tiles (rows 0..511; the last tile runs past the image, those rows are never read back)
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc_bf16(128, 32, 0, 0);
+            const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+            for (int tile = 0; tile < 4; ++tile) {
+                uint32_t a_lo = desc_lo(smem_u32(img) + (uint32_t)tile * 128 * 16, (uint32_t)HU_ROWS * 16);
+                uint32_t b_lo = desc_lo(smem_u32(bw), 32 * 16);
+                for (int ks = 0; ks < (p.C >> 4); ++ks, a_lo += 2 * HU_ROWS, b_lo += 2 * 32)
+                    mma_bf16(tmem_base + 384 + tile * 32, desc_join(a_lo, a_hi), desc_join(b_lo, b_hi), idesc, ks != 0);
+            }
+            mma_commit(&bar_mma);
+        }
+        __syncwarp();
+    }
+    mbar_wait(&bar_mma, 0);
+    tc_fence_after();
+    {
+        // warp w reads TMEM lanes 32*(w%4)..: tiles w/4 (0..2), and tile 3 again by warps 0..3
+        const int q = warp & 3;
+        for (int tile = warp >> 2; tile < 4; tile += 3) {
+            const int row = tile * 128 + q * 32 + lane;
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 384 + tile * 32, r);
+            tmem_ld_wait();
+            if (row < HU_ROWS) {
+#pragma unroll
+                for (int t = 0; t < 9; ++t) gs[row * 9 + t] = __uint_as_float(r[t]) + __uint_as_float(r[9 + t]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    HSTAMP(2);
+
+    // ---- logits, log-softmax, NLL, top-1: one thread per image row 21..404
+    const int rho = 21 + tid;
+    const int xp = rho / 20, yp = rho - xp * 20;
+    const int x = xp - 1, y = yp - 1;
+    const bool valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
+    const int pt = x * DG_BOARD + y;
+    float z = 0.f;
+    if (valid) {
+        float acc = 0.f;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) acc += gs[(rho + (t / 3 - 1) * 20 + (t % 3 - 1)) * 9 + t];
+        z = acc + p.b[0] + p.a[pt];
+    }
+    const float h = valid ? fmaxf(z, 0.f) : -INFINITY;           // ReLU stays before LogSoftMax (experiments.lua:147)
+    const float mx = block_reduce_max(h, red);
+    const float se = block_reduce_sum(valid ? expf(h - mx) : 0.f, red);
+    const float lse = mx + logf(se);
+    const float lp = h - lse;
+    if (valid) p.logp[(size_t)pos * DG_POINTS + pt] = lp;
+    {
+        int cand = (valid && h == mx) ? pt : 0x7fffffff;          // first index of the maximum
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, s));
+        if (lane == 0) redi[warp] = cand;
+        __syncthreads();
+        if (tid == 0) {
+            int bst = redi[0];
+            for (int w = 1; w < 12; ++w) bst = min(bst, redi[w]);
+            if (p.argmax) p.argmax[pos] = bst;
+        }
+        __syncthreads();
+    }
+    const int tgt = p.targets ? p.targets[pos] : -1;
+    if (valid && pt == tgt && p.loss_n) p.loss_n[pos] = -lp;
+    HSTAMP(3);
+    if (p.dz_out) {
+        // ---- backward of LogSoftMax + NLL + ReLU on the 1-channel map
+        float dzv = 0.f;
+        if (valid && z > 0.f) dzv = p.scale * (expf(lp) - (pt == tgt ? 1.f : 0.f));
+        dzs[32 + rho] = dzv;
+        float *part = p.part + (size_t)pos * (9 * p.C + DG_POINTS);
+        if (valid) part[9 * p.C + pt] = dzv;                     // nn.Add gradBias (361) and conv gradBias (1) are sums of these over positions
+        __syncthreads();
+        // shifted dz columns: dzim[row][j] = hi/lo of dz[row - off(t)]
+        for (int row = tid; row < HU_ROWS; row += blockDim.x) {
+            __align__(16) bf16 col[32];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) {
+                const float d = dzs[32 + row - ((t / 3 - 1) * 20 + (t % 3 - 1))];
+                const bf16 hh = __float2bfloat16(d);
+                col[t] = hh; col[18 + t] = hh;
+                col[9 + t] = __float2bfloat16(d - __bfloat162float(hh));
+            }
+#pragma unroll
+            for (int j = 27; j < 32; ++j) col[j] = __float2bfloat16(0.f);
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                *reinterpret_cast<uint4 *>(dzim + ((size_t)g * HU_ROWS + row) * 16) = *reinterpret_cast<const uint4 *>(col + 8 * g);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        if (warp == 0) {
+            if (elect_one()) {
+                // gW: M = channels (MN-major image, 16 chunks), N = 32 tap columns (MN-major dzim), K = all 432 rows
+                const uint32_t idesc_w = make_idesc_bf16(128, 32, 1, 1);
+                const uint32_t hi_mn = desc_hi((uint32_t)HU_ROWS * 16);
+                uint32_t a_lo = desc_lo(smem_u32(img), 128), b_lo = desc_lo(smem_u32(dzim), 128);
+                for (int ks = 0; ks < HU_ROWS / 16; ++ks, a_lo += 16, b_lo += 16)
+                    mma_bf16(tmem_base + 384, desc_join(a_lo, hi_mn), desc_join(b_lo, hi_mn), idesc_w, ks != 0);
+                // dZ: M = rows 21 + 128*tile, K = 32 tap columns (K-major dzim), N = C channels (K-major b2)
+                const uint32_t idesc_d = make_idesc_bf16(128, p.C, 0, 0);
+                const uint32_t hi_k = desc_hi(128);
+                for (int tile = 0; tile < 3; ++tile) {
+                    uint32_t a2 = desc_lo(smem_u32(dzim) + (uint32_t)(21 + tile * 128) * 16, (uint32_t)HU_ROWS * 16);
+                    uint32_t bb = desc_lo(smem_u32(b2), 128 * 16);
+                    for (int ks = 0; ks < 2; ++ks, a2 += 2 * HU_ROWS, bb += 2 * 128)
+                        mma_bf16(tmem_base + tile * p.C, desc_join(a2, hi_k), desc_join(bb, hi_k), idesc_d, ks != 0);
+                }
+                mma_commit(&bar_mma);
+            }
+            __syncwarp();
+        }
+        mbar_wait(&bar_mma, 1);
+        tc_fence_after();
+        HSTAMP(4);
+        const int q = warp & 3;
+        if (warp < 4) {
+            // weight gradient of the last layer: lane = input channel
+            const int ci = q * 32 + lane;
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + 384, r);
+            tmem_ld_wait();
+            if (ci < p.C) {
+#pragma unroll
+                for (int t = 0; t < 9; ++t) part[ci * 9 + t] = __uint_as_float(r[t]) + __uint_as_float(r[9 + t]);   // Torch7 order of W[0][ci][ky][kx]
+            }
+        }
+        {
+            // dZ_{L-1}: warp w drains tile w/4, its lane quarter; ReLU mask from the image in shared memory
+            const int tile = warp >> 2;
+            const int ro = 21 + tile * 128 + q * 32 + lane;
+            const int xq = ro / 20 - 1, yq = ro - (ro / 20) * 20 - 1;
+            const bool ok = xq >= 0 && xq < DG_BOARD && yq >= 0 && yq < DG_BOARD;
+            const int rho_out = (xq + p.pad_out) * p.pitch_out + yq + p.pad_out;
+            const __nv_bfloat162 zero2 = __floats2bfloat162_rn(0.f, 0.f);
+            for (int c0 = 0; c0 < p.C; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + tile * p.C + c0, r);
+                tmem_ld_wait();
+                if (ok) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        const int chunk = (c0 >> 3) + g;
+                        const uint4 hv = *reinterpret_cast<const uint4 *>(img + ((size_t)chunk * HU_ROWS + ro) * 16);
+                        const uint32_t hw[4] = {hv.x, hv.y, hv.z, hv.w};
+                        uint32_t w[4];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(r[g * 8 + 2 * j]), __uint_as_float(r[g * 8 + 2 * j + 1]));
+                            w[j] = *reinterpret_cast<const uint32_t *>(&t2) & __hgt2_mask(*reinterpret_cast<const __nv_bfloat162 *>(&hw[j]), zero2);
+                        }
+                        *reinterpret_cast<uint4 *>(p.dz_out + (((size_t)pos * chunks + chunk) * p.R_out + rho_out) * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+                    }
+                }
+            }
+        }
+        HSTAMP(5);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+    DG_TL_OUT(p.tl, DG_TL_HEAD);
+}
+
 // gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order.
 // A block owns 32 columns; its 8 warps take the positions n = w, w+8, .. and the partial sums meet in shared memory.
 __global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__restrict__ part, int n, int C, float *__restrict__ gW,
@@ -1616,6 +1849,7 @@ int dg_bf16_create(dg_model *m) {
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
     DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
     DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
+    DG_CUDA(cudaFuncSetAttribute(head_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 8192));
     return 0;
 }
 
@@ -1728,8 +1962,13 @@ static int launch_head(dg_model *m, bool backward, float scale) {
     hp.scale = scale;
     const size_t smem = (((size_t)(m->C / 8) * DG_R3 * 16 + 1023) & ~(size_t)1023) + (size_t)18 * m->C * 4;
     DG_REQUIRE(smem <= 227 * 1024 - 4096, "bf16 path: head image does not fit shared memory (C=%d)", m->C);
+    // C <= 128: the tensor-core head (three small GEMMs); wider nets keep the SIMT kernel (3 x C accumulator columns exceed TMEM)
+    static const bool simt_head = getenv("DG_SIMT_HEAD") != nullptr;
+    const bool umma_head = !simt_head && m->C <= 128 && m->C % 16 == 0;
+    const size_t smem_u = (size_t)16 * DG_R3 * 16 + 2048 + 16 * 32 * 16 + 4 * 128 * 16 + 4 * DG_R3 * 16 + (size_t)DG_R3 * 9 * 4;
     { dg_prof_scope _ps(c, DG_K_HEAD);
-    DG_CUDA(dg_launch_pdl(head_bf16_kernel, dim3(m->n), dim3(384), smem, c->stream, hp));
+    if (umma_head) DG_CUDA(dg_launch_pdl(head_umma_kernel, dim3(m->n), dim3(384), smem_u, c->stream, hp));
+    else DG_CUDA(dg_launch_pdl(head_bf16_kernel, dim3(m->n), dim3(384), smem, c->stream, hp));
     }
     c->launches++;
     if (hp.dbg && backward) {
