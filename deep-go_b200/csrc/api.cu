@@ -466,13 +466,8 @@ extern "C" int dg_sgd_step(dg_model *m, float rate) {
 // one fused step on the context's stream: eval() of train.lua:4-12 followed by SGD:step (train.lua:131)
 static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
     dg_ctx *c = m->ctx;
-    if (m->bf && dg_bf16_defers_grads(m)) {
-        // the conv layers' gradient goes from the accumulation buffers straight into the SGD kernel: only the head's slice is summed in place
-        const LayerInfo &lh = m->layers[m->L - 1];
-        DG_CUDA(cudaMemsetAsync(m->grads + lh.offW, 0, (m->P - lh.offW) * 4, c->stream));
-    } else {
-        DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));      // train.lua:5
-    }
+    // a deferring bf16 step keeps the whole gradient in the accumulation buffers (cleared inside the backward pass)
+    if (!(m->bf && dg_bf16_defers_grads(m))) DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));      // train.lua:5
     m->fused_step = true;
     int rc = forward_impl(m);                                              // train.lua:6
     if (!rc) rc = backward_impl(m);                                        // train.lua:8-10
@@ -489,6 +484,7 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     DG_CUDA(cudaSetDevice(c->dev));
     DG_REQUIRE(m->have_targets, "dg_train_step: the staged batch has no targets");
     DG_REQUIRE(m->n > 0, "dg_train_step: no batch staged");
+    if (m->bf) if (int rc = dg_bf16_dp_prepare(m)) return rc;
     static const bool no_graph = getenv("DG_NO_GRAPH") != nullptr || getenv("DG_TIMELINE") != nullptr;
     // with data parallelism the NCCL allreduce is captured too (the communication stream joins the capture through events)
     static const bool no_dp_graph = getenv("DG_NO_DP_GRAPH") != nullptr;

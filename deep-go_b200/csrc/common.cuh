@@ -60,11 +60,12 @@ struct dg_ctx {
     int rank = 0, world = 1;
     cudaStream_t comm_stream = nullptr;
     cudaEvent_t ev_grad_ready = nullptr, ev_comm_done = nullptr;
+    bool dp_pending = false;           // buckets issued on the communication stream since the last dg_dp_finish
     // DG_TL=1: device buffer of globaltimer stamps {first CTA in, first CTA past the dependency wait, last CTA out} per kernel of the
     // step -- the only clock that sees inside a replayed CUDA graph (dg_prof_timeline)
     unsigned long long *tl = nullptr;
 };
-enum { DG_TL_CONV0 = 0, DG_TL_CONV, DG_TL_HEAD, DG_TL_DGRAD, DG_TL_WGRAD, DG_TL_WGRAD0, DG_TL_FINALIZE, DG_TL_SGD, DG_TL_HEADRED, DG_TL_COUNT };
+enum { DG_TL_CONV0 = 0, DG_TL_CONV, DG_TL_HEAD, DG_TL_DGRAD, DG_TL_WGRAD, DG_TL_WGRAD0, DG_TL_FINALIZE, DG_TL_SGD, DG_TL_HEADRED, DG_TL_P2P, DG_TL_COUNT };
 
 struct LayerInfo {
     int cin, cout, k;
@@ -150,3 +151,9 @@ int dg_launch_fill(dg_ctx *ctx, float *p, size_t n, float v);
 // ---- dp.cu
 int dg_dp_bucket(dg_ctx *ctx, float *buf, size_t n, cudaStream_t producer = nullptr);
 int dg_dp_finish(dg_ctx *ctx);
+// gradient exchange over NVLink peer memory (dp.cu): collective setup, then one kernel per step
+#define DG_MAX_RANKS 8
+struct dg_p2p;
+int dg_dp_p2p_setup(dg_ctx *ctx, float *buf, size_t nfloats, dg_p2p **out);
+int dg_dp_p2p_allreduce(dg_ctx *ctx, dg_p2p *p);
+void dg_dp_p2p_destroy(dg_p2p *p);

@@ -1455,6 +1455,7 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
                                                        int R_out, int pitch_out, int pad_out, int smem_row, unsigned long long *tl) {
     extern __shared__ float wrow[];                 // [CO_B][smem_row]: the block's updated weight rows
     __shared__ float bnew[CO_B], bsum[CO_B];
+    __shared__ float bpart[(CO_B * DG_POINTS + NT - 1) / NT][NT / 32][2];   // per-warp partial sums of the per-point bias gradient
     dg_pdl_launch_dependents();
     DG_TL_IN(tl, DG_TL_SGD);
     dg_pdl_wait();
@@ -1510,16 +1511,14 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
         }
         if (from_acc) {
             // conv gradBias = sum over the points of nn.Add's gradBias.  A warp spans at most two channels (361 > 32): two shuffle
-            // reductions, then one shared-memory add per channel and warp (every thread adding to a handful of words directly serialises)
+            // reductions per warp; the per-warp partial sums are added in a fixed order below (data-parallel replicas must stay
+            // bit-identical, so no floating-point atomics here)
             const int r_lo = (int)((threadIdx.x & ~31u) + k * NT) / DG_POINTS;
             const int r_me = i / DG_POINTS;
             float s_lo = (i < nco * DG_POINTS && r_me == r_lo) ? ag[k] : 0.f, s_hi = (i < nco * DG_POINTS && r_me != r_lo) ? ag[k] : 0.f;
 #pragma unroll
             for (int sh = 16; sh > 0; sh >>= 1) { s_lo += __shfl_xor_sync(0xffffffffu, s_lo, sh); s_hi += __shfl_xor_sync(0xffffffffu, s_hi, sh); }
-            if ((threadIdx.x & 31) == 0) {
-                if (r_lo < nco) atomicAdd(&bsum[r_lo], s_lo);
-                if (r_lo + 1 < nco) atomicAdd(&bsum[r_lo + 1], s_hi);
-            }
+            if ((threadIdx.x & 31) == 0) { bpart[k][threadIdx.x >> 5][0] = s_lo; bpart[k][threadIdx.x >> 5][1] = s_hi; }
         }
     }
     for (int base = threadIdx.x; base < total; base += 12 * NT) {
@@ -1544,7 +1543,20 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
             }
         }
     }
-    if (from_acc) __syncthreads();                  // bsum complete
+    if (from_acc) {
+        __syncthreads();
+        if (threadIdx.x < nco) {
+            float t = 0.f;
+            for (int k = 0; k < NB; ++k)
+                for (int w = 0; w < NT / 32; ++w) {
+                    const int r_lo = (w * 32 + k * NT) / DG_POINTS;
+                    if (r_lo == (int)threadIdx.x) t += bpart[k][w][0];
+                    else if (r_lo + 1 == (int)threadIdx.x) t += bpart[k][w][1];
+                }
+            bsum[threadIdx.x] = t;
+        }
+        __syncthreads();
+    }
     if (threadIdx.x < nco) {
         const float v = fmaf(neg_rate, from_acc ? bsum[threadIdx.x] : L.gb[co0 + threadIdx.x], L.b[co0 + threadIdx.x]);
         L.b[co0 + threadIdx.x] = v;
@@ -1617,6 +1629,8 @@ struct Bf16Path {
     SgdPackLayer *sgd_table = nullptr;     // device copy, one entry per layer (the 1-channel last layer included)
     SgdPackLayer *sgd_table_acc = nullptr; // same, conv layers reading the accumulation buffers (fused step)
     std::vector<SgdPackLayer> sgd_host;
+    dg_p2p *p2p = nullptr;                 // data parallel: the peers' accumulation buffers mapped over NVLink (NULL: NCCL)
+    bool p2p_tried = false;
     bool defer_grads = false;              // fused steps hand the conv gradients to the SGD kernel in the accumulation buffers
     bool grads_pending = false;            // the conv layers' gradient of the last fused step is still in gacc / gab, not in m->grads
     int sgd_smem_row = 0, sgd_max_co8 = 0;
@@ -1626,6 +1640,7 @@ struct Bf16Path {
     std::vector<size_t> gab_off;           // bias-gradient accumulation buffers, same allocation
     bool fused_bias = false;               // bias gradients come out of the weight-gradient kernel
     size_t gacc_floats = 0;
+    size_t head_n = 0;                     // floats of the head layer's gradient (gW, gb, ga), the first block of gacc
     bool deterministic = false;            // DG_DETERMINISTIC=1: partial tiles + ordered reduction instead of L2 reductions
     float *scratch = nullptr;              // weight-gradient partial tiles, two halves used alternately
     size_t scratch_bytes = 0;              // bytes of one half
@@ -1812,16 +1827,23 @@ int dg_bf16_create(dg_model *m) {
         DG_CUDA(cudaStreamSynchronize(st));
     }
     b->deterministic = getenv("DG_DETERMINISTIC") != nullptr;
+    // Accumulation buffers, one allocation cleared by one memset: [head layer gradient | layer 0: weights, bias | layer 1: .. ].
+    // Each layer's block is contiguous, so a data-parallel bucket is a range of layers; the head block (gW, gb, ga in Torch7
+    // order) lets a fused step exchange everything in the buckets' own order.
     b->gacc_off.assign(L - 1, 0);
-    for (int l = 0; l < L - 1; ++l) { b->gacc_off[l] = b->gacc_floats; b->gacc_floats += (size_t)m->layers[l].k * m->layers[l].k * b->ops[l].cin_pad * m->layers[l].cout; }
-    // bias-gradient accumulation buffers behind them (same memset): the weight-gradient kernel needs the spare TMEM columns
     b->gab_off.assign(L - 1, 0);
     b->fused_bias = !b->deterministic;
+    {
+        const LayerInfo &lh = m->layers[L - 1];
+        b->head_n = lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS;
+        b->gacc_floats = (b->head_n + 3) & ~(size_t)3;
+    }
     for (int l = 0; l < L - 1; ++l) {
         const Geom &gl = l == 0 ? b->g_first : b->g3;
         WgradPlan wpl;
         if (int rc = wgrad_plan(m, b->ops[l].cin_pad, m->layers[l].cout, m->layers[l].k, gl, wpl)) return rc;
         if (m->layers[l].k * wpl.nb + WG_RP > 512 || wpl.splits % (gl.ntiles * 128 / WG_RP) != 0) b->fused_bias = false;
+        b->gacc_off[l] = b->gacc_floats; b->gacc_floats += (size_t)m->layers[l].k * m->layers[l].k * b->ops[l].cin_pad * m->layers[l].cout;
         b->gab_off[l] = b->gacc_floats; b->gacc_floats += (size_t)gl.ntiles * 128 * m->layers[l].cout;
     }
     DG_CUDA(cudaMalloc((void **)&b->gacc, b->gacc_floats * 4));
@@ -1833,6 +1855,10 @@ int dg_bf16_create(dg_model *m) {
             const Geom &gl = l == 0 ? b->g_first : b->g3;
             sa[l].gacc = b->gacc + b->gacc_off[l]; sa[l].gab = b->gacc + b->gab_off[l];
             sa[l].g_pitch = gl.pitch; sa[l].g_pad = gl.pad; sa[l].g_first = gl.first;
+        }
+        {
+            const LayerInfo &lh = m->layers[L - 1];
+            sa[L - 1].gW = b->gacc; sa[L - 1].gb = b->gacc + lh.nW; sa[L - 1].ga = b->gacc + lh.nW + lh.cout;
         }
         DG_CUDA(cudaMemcpyAsync(b->sgd_table_acc, sa.data(), sa.size() * sizeof(SgdPackLayer), cudaMemcpyHostToDevice, st));
     }
@@ -1866,6 +1892,7 @@ void dg_bf16_destroy(dg_model *m) {
     cudaFree(b->fin_table);
     cudaFree(b->sgd_table);
     cudaFree(b->sgd_table_acc);
+    dg_dp_p2p_destroy(b->p2p);
     cudaFree(b->head_part);
     if (b->side) cudaStreamDestroy(b->side);
     delete b;
@@ -1898,6 +1925,22 @@ int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev) {
     return 0;
 }
 
+// data parallel, first fused step (a collective: every rank gets here): map the peers' accumulation buffers.  Falls back to NCCL
+// (with the reason on stderr, once) when CUDA IPC or peer access is unavailable; DG_DP_NCCL=1 forces NCCL.
+int dg_bf16_dp_prepare(dg_model *m) {
+    Bf16Path *b = m->bf;
+    dg_ctx *c = m->ctx;
+    if (c->world <= 1 || b->p2p_tried || !b->defer_grads) return 0;
+    b->p2p_tried = true;
+    if (getenv("DG_DP_NCCL")) return 0;
+    DG_CUDA(cudaStreamSynchronize(c->stream));
+    if (dg_dp_p2p_setup(c, b->gacc, b->gacc_floats, &b->p2p) != 0) {
+        fprintf(stderr, "deepgo_b200: %s\n", dg_last_error());
+        b->p2p = nullptr;
+    }
+    return 0;
+}
+
 // materialise the conv layers' gradient of the last fused step in the Torch7-order vector (no-op when it already is there)
 int dg_bf16_sync_grads(dg_model *m) {
     Bf16Path *b = m->bf;
@@ -1907,6 +1950,7 @@ int dg_bf16_sync_grads(dg_model *m) {
     DG_CUDA(cudaMemsetAsync(m->grads + l0.offW, 0, (lh.offW - l0.offW) * 4, c->stream));
     wgrad_finalize_kernel<<<dim3(96, m->L - 1), 256, FIN_SMEM_FLOATS * 4, c->stream>>>(b->fin_table, nullptr);
     c->launches++;
+    DG_CUDA(cudaMemcpyAsync(m->grads + lh.offW, b->gacc, b->head_n * 4, cudaMemcpyDeviceToDevice, c->stream));
     DG_CUDA(cudaGetLastError());
     b->grads_pending = false;
     return 0;
@@ -2060,6 +2104,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
     DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
     if (!b->deterministic) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_memset, 0));     // the weight-gradient kernels add into the cleared buffers
     bool rec_reduce[2] = {false, false};   // events recorded in THIS pass (stream capture forbids waiting on older records)
+    int dp_done_from = m->L - 1;           // conv layers >= this index already left in a data-parallel bucket
     static long long *wdbg = nullptr;
     static const bool wtl = getenv("DG_TIMELINE") != nullptr;
     if (wtl && !wdbg) cudaMalloc(&wdbg, 148 * 8 * sizeof(long long));
@@ -2067,8 +2112,11 @@ int dg_bf16_backward(dg_model *m, float scale) {
         const LayerInfo &lh = m->layers[m->L - 1];
         cudaStream_t hst = b->side;
         dg_prof_scope _ps(c, DG_K_HEAD, hst);
-        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, hst>>>(b->head_part, m->n, m->C, m->grads + lh.offW,
-                                                                                       m->grads + lh.offB, m->grads + lh.offA);
+        // a deferring fused step sums the head layer's gradient into the head block of the accumulation buffers
+        const bool to_acc = m->fused_step && b->defer_grads;
+        float *hW = to_acc ? b->gacc : m->grads + lh.offW, *hb = to_acc ? b->gacc + lh.nW : m->grads + lh.offB;
+        float *ha = to_acc ? b->gacc + lh.nW + lh.cout : m->grads + lh.offA;
+        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, hst>>>(b->head_part, m->n, m->C, hW, hb, ha);
         c->launches++;
     }
     // bias gradients of every conv layer: side stream, all dZ are ready
@@ -2091,6 +2139,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
         if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
         int nl = 1;
         if (!b->deterministic && l >= 1) nl = std::min(l, WG_MAX_LAYERS);       // layers l, l-1, .., l-nl+1 (all >= 1)
+        // (data parallel: splitting this launch so that the upper layers' bucket overlaps the lower layers' weight gradients was
+        // measured slower -- NCCL's CTAs take shared memory on SMs the persistent kernel needs all of, its CTAs then run in two waves)
+        const bool dp_split = false;
         const int par = l & 1;
         float *scratch = b->scratch + (size_t)par * (b->scratch_bytes / 4);
         WgradParams wp{};
@@ -2138,6 +2189,13 @@ int dg_bf16_backward(dg_model *m, float scale) {
         }
         DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
         rec_reduce[par] = true;
+        if (dp_split && l == m->L - 2 && l - nl >= 1) {
+            // bucket of the layers this launch finished: their blocks are contiguous (ascending layer index)
+            const int lo = l - nl + 1;
+            const size_t end = l + 1 < m->L - 1 ? b->gacc_off[l + 1] : b->gacc_floats;
+            if (int rc = dg_dp_bucket(c, b->gacc + b->gacc_off[lo], end - b->gacc_off[lo])) return rc;
+            dp_done_from = lo;
+        }
         l -= nl;
     }
     // Inside dg_train_step the SGD kernel reads the accumulation buffers itself: the Torch7-order gradient vector is not
@@ -2159,8 +2217,10 @@ int dg_bf16_backward(dg_model *m, float scale) {
         const LayerInfo &l0 = m->layers[0], &lh = m->layers[m->L - 1];
         const size_t head_n = lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS;
         if (defer) {
-            if (int rc = dg_dp_bucket(c, b->gacc, b->gacc_floats)) return rc;
-            if (int rc = dg_dp_bucket(c, m->grads + lh.offW, head_n)) return rc;
+            // head block + the conv layers not exchanged yet: one contiguous range from the start of the allocation
+            const size_t end = dp_done_from < m->L - 1 ? b->gacc_off[dp_done_from] : b->gacc_floats;
+            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p)) return rc; }        // one kernel over NVLink peer memory
+            else if (int rc = dg_dp_bucket(c, b->gacc, end)) return rc;
         } else {
             if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + head_n - l0.offW)) return rc;
         }

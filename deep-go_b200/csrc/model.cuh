@@ -40,6 +40,7 @@ int dg_bf16_stage_planes(dg_model *m);                   // act[0] (fp32 NCHW) -
 int dg_bf16_stage_raw(dg_model *m);                      // raw records -> blocked bf16 input image
 int dg_bf16_forward(dg_model *m);                        // fills m->d_logp-ready logits via head
 int dg_bf16_backward(dg_model *m, float scale);
+int dg_bf16_dp_prepare(dg_model *m);                     // data parallel: map the peers' gradient buffers before the first fused step
 int dg_bf16_sync_grads(dg_model *m);                     // fused step leaves the conv gradients in accumulation buffers: fold them into m->grads
 bool dg_bf16_defers_grads(const dg_model *m);            // fused steps keep the conv gradients in the accumulation buffers
 void dg_bf16_after_fused_step(dg_model *m);              // host-side state after a (replayed) fused step
