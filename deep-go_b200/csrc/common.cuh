@@ -65,7 +65,7 @@ struct dg_ctx {
     // step -- the only clock that sees inside a replayed CUDA graph (dg_prof_timeline)
     unsigned long long *tl = nullptr;
 };
-enum { DG_TL_CONV0 = 0, DG_TL_CONV, DG_TL_HEAD, DG_TL_DGRAD, DG_TL_WGRAD, DG_TL_WGRAD0, DG_TL_FINALIZE, DG_TL_SGD, DG_TL_HEADRED, DG_TL_P2P, DG_TL_COUNT };
+enum { DG_TL_CONV0 = 0, DG_TL_CONV, DG_TL_HEAD, DG_TL_DGRAD, DG_TL_WGRAD, DG_TL_WGRAD0, DG_TL_FINALIZE, DG_TL_SGD, DG_TL_HEADRED, DG_TL_P2P, DG_TL_P2P_B, DG_TL_COUNT };
 
 struct LayerInfo {
     int cin, cout, k;
@@ -155,5 +155,5 @@ int dg_dp_finish(dg_ctx *ctx);
 #define DG_MAX_RANKS 8
 struct dg_p2p;
 int dg_dp_p2p_setup(dg_ctx *ctx, float *buf, size_t nfloats, dg_p2p **out);
-int dg_dp_p2p_allreduce(dg_ctx *ctx, dg_p2p *p);
+int dg_dp_p2p_allreduce(dg_ctx *ctx, dg_p2p *p, cudaStream_t st, size_t off_floats, size_t n_floats, int chan);
 void dg_dp_p2p_destroy(dg_p2p *p);

@@ -2139,9 +2139,6 @@ int dg_bf16_backward(dg_model *m, float scale) {
         if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
         int nl = 1;
         if (!b->deterministic && l >= 1) nl = std::min(l, WG_MAX_LAYERS);       // layers l, l-1, .., l-nl+1 (all >= 1)
-        // (data parallel: splitting this launch so that the upper layers' bucket overlaps the lower layers' weight gradients was
-        // measured slower -- NCCL's CTAs take shared memory on SMs the persistent kernel needs all of, its CTAs then run in two waves)
-        const bool dp_split = false;
         const int par = l & 1;
         float *scratch = b->scratch + (size_t)par * (b->scratch_bytes / 4);
         WgradParams wp{};
@@ -2189,13 +2186,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
         }
         DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
         rec_reduce[par] = true;
-        if (dp_split && l == m->L - 2 && l - nl >= 1) {
-            // bucket of the layers this launch finished: their blocks are contiguous (ascending layer index)
-            const int lo = l - nl + 1;
-            const size_t end = l + 1 < m->L - 1 ? b->gacc_off[l + 1] : b->gacc_floats;
-            if (int rc = dg_dp_bucket(c, b->gacc + b->gacc_off[lo], end - b->gacc_off[lo])) return rc;
-            dp_done_from = lo;
-        }
+        // (data parallel: exchanging the 3x3 layers' blocks on the side stream under the first layer's weight-gradient kernel was
+        // measured: the exchange kernel's fixed cost -- two cross-GPU barriers and an NVLink round trip each way, ~17 us -- is then
+        // paid twice and the tail of the overlapped launch still sticks out; one exchange after the last kernel is shorter)
         l -= nl;
     }
     // Inside dg_train_step the SGD kernel reads the accumulation buffers itself: the Torch7-order gradient vector is not
@@ -2219,7 +2212,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         if (defer) {
             // head block + the conv layers not exchanged yet: one contiguous range from the start of the allocation
             const size_t end = dp_done_from < m->L - 1 ? b->gacc_off[dp_done_from] : b->gacc_floats;
-            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p)) return rc; }        // one kernel over NVLink peer memory
+            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p, c->stream, 0, end, 1)) return rc; }   // one kernel over NVLink peer memory
             else if (int rc = dg_dp_bucket(c, b->gacc, end)) return rc;
         } else {
             if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + head_n - l0.offW)) return rc;

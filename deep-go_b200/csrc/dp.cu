@@ -104,24 +104,27 @@ struct P2PSignals {                          // lives in every rank's IPC-shared
 };
 struct P2PArgs {
     float *buf[DG_MAX_RANKS];                // every rank's accumulation buffer as mapped HERE (buf[rank] is the local one)
-    P2PSignals *sig[DG_MAX_RANKS];
+    P2PSignals *sig[DG_MAX_RANKS];           // [2] signal sets per rank
     int rank, world;
-    size_t n4;                               // float4 elements in the buffer
+    size_t off4, n4;                         // float4 range of the buffer this launch exchanges
+    int chan;                                // signal set: launches that may overlap on a GPU use different ones
     unsigned long long *tl;                  // optional step timeline (DG_TL=1)
 };
 
 __device__ __forceinline__ void p2p_st_release_sys(unsigned int *p, unsigned int v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ unsigned int p2p_ld_acquire_sys(const unsigned int *p) { unsigned int v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
-__device__ __forceinline__ float4 p2p_ld_v4(const float4 *p) { float4 v; asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory"); return v; }
-__device__ __forceinline__ void p2p_st_v4(float4 *p, float4 v) { asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory"); }
+// data moves with plain weak accesses (L2-level: nothing of these buffers can be stale in L1, each address is touched once per
+// launch, after the barrier); ordering comes from the barriers' fence + release/acquire at system scope
+__device__ __forceinline__ float4 p2p_ld_v4(const float4 *p) { return __ldcg(p); }
+__device__ __forceinline__ void p2p_st_v4(float4 *p, float4 v) { __stcg(p, v); }
 
 // all ranks' block b meet: thread r tells rank r, then waits for rank r's word in the local buffer (bounded: a dead peer traps)
 __device__ __forceinline__ void p2p_barrier(const P2PArgs &a, unsigned int (P2PSignals::*which)[DG_P2P_BLOCKS][DG_MAX_RANKS], unsigned int call) {
     __syncthreads();
     if (threadIdx.x < (unsigned)a.world) {
         __threadfence_system();
-        p2p_st_release_sys(&(a.sig[threadIdx.x]->*which)[blockIdx.x][a.rank], call);
-        const unsigned int *mine = &(a.sig[a.rank]->*which)[blockIdx.x][threadIdx.x];
+        p2p_st_release_sys(&((a.sig[threadIdx.x] + a.chan)->*which)[blockIdx.x][a.rank], call);
+        const unsigned int *mine = &((a.sig[a.rank] + a.chan)->*which)[blockIdx.x][threadIdx.x];
         unsigned long long spins = 0;
         while (p2p_ld_acquire_sys(mine) != call)
             if (++spins > (1ull << 31)) __trap();
@@ -131,16 +134,19 @@ __device__ __forceinline__ void p2p_barrier(const P2PArgs &a, unsigned int (P2PS
 
 __global__ void __launch_bounds__(512) p2p_allreduce_kernel(const __grid_constant__ P2PArgs a) {
     __shared__ unsigned int call_s;
-    DG_TL_IN(a.tl, DG_TL_P2P);
-    if (threadIdx.x == 0) call_s = ++a.sig[a.rank]->calls[blockIdx.x];
+    dg_pdl_launch_dependents();              // the SGD kernel may take its SMs early; it waits for this grid before it reads
+    DG_TL_IN(a.tl, DG_TL_P2P + a.chan);
+    dg_pdl_wait();                           // launched under the tail of the last weight-gradient kernel
+    if (threadIdx.x == 0) call_s = ++(a.sig[a.rank] + a.chan)->calls[blockIdx.x];
     __syncthreads();
     const unsigned int call = call_s;
     // every rank has finished its weight-gradient kernels (stream order on each GPU) before anybody reads its buffer
     p2p_barrier(a, &P2PSignals::begin, call);
-    DG_TL_GO(a.tl, DG_TL_P2P);
+    DG_TL_GO(a.tl, DG_TL_P2P + a.chan);
     const size_t per = (a.n4 + a.world - 1) / a.world;
-    const size_t lo = per * a.rank, hi = lo + per < a.n4 ? lo + per : a.n4;
-    // every thread first issues the loads of two elements from ALL ranks (they overlap on the wire), then adds in rank order
+    const size_t lo = a.off4 + (per * a.rank < a.n4 ? per * a.rank : a.n4), hi = a.off4 + (per * (a.rank + 1) < a.n4 ? per * (a.rank + 1) : a.n4);
+    // every thread first issues the loads of two elements from ALL ranks (they overlap on the wire), then adds in rank order.
+    // (Measured on 2 GPUs: more loads in flight per thread, or more threads, do not shorten this phase -- 24 us for 8.7 MB.)
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += 2 * stride) {
         const size_t i2 = i + stride;
@@ -168,7 +174,7 @@ __global__ void __launch_bounds__(512) p2p_allreduce_kernel(const __grid_constan
     }
     // nobody leaves (and lets its next kernel read, or its next step clear, the buffer) before every rank has written every slice
     p2p_barrier(a, &P2PSignals::end, call);
-    DG_TL_OUT(a.tl, DG_TL_P2P);
+    DG_TL_OUT(a.tl, DG_TL_P2P + a.chan);
 }
 
 struct dg_p2p {
@@ -185,8 +191,8 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
     DG_REQUIRE(c->world > 1 && c->world <= DG_MAX_RANKS && c->comm && p_allgather, "peer exchange: needs 2..%d ranks and ncclAllGather", DG_MAX_RANKS);
     DG_REQUIRE(nfloats % 4 == 0, "peer exchange: buffer length must be a multiple of 4 floats");
     dg_p2p *p = new dg_p2p();
-    DG_CUDA(cudaMalloc((void **)&p->sig_local, sizeof(P2PSignals)));
-    DG_CUDA(cudaMemset(p->sig_local, 0, sizeof(P2PSignals)));
+    DG_CUDA(cudaMalloc((void **)&p->sig_local, 2 * sizeof(P2PSignals)));
+    DG_CUDA(cudaMemset(p->sig_local, 0, 2 * sizeof(P2PSignals)));
     struct Rec { cudaIpcMemHandle_t buf, sig; int dev; int ok; };
     Rec mine{}; mine.dev = c->dev; mine.ok = 1;
     if (cudaIpcGetMemHandle(&mine.buf, buf) != cudaSuccess || cudaIpcGetMemHandle(&mine.sig, p->sig_local) != cudaSuccess) { cudaGetLastError(); mine.ok = 0; }
@@ -232,7 +238,7 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
         dg_dp_p2p_destroy(p);
         DG_REQUIRE(false, "peer exchange: a rank could not map its peers' memory (CUDA IPC / P2P unavailable): using NCCL");
     }
-    p->args.rank = c->rank; p->args.world = c->world; p->args.n4 = nfloats / 4;
+    p->args.rank = c->rank; p->args.world = c->world; p->args.off4 = 0; p->args.n4 = nfloats / 4; p->args.chan = 0;
     *out = p;
     return 0;
 }
@@ -244,11 +250,13 @@ void dg_dp_p2p_destroy(dg_p2p *p) {
     delete p;
 }
 
-// sum the mapped buffers over ranks, in place on every rank, on the context's stream (captured into the step graph like any kernel)
-int dg_dp_p2p_allreduce(dg_ctx *c, dg_p2p *p) {
-    p->args.tl = c->tl;
-    p2p_allreduce_kernel<<<DG_P2P_BLOCKS, 512, 0, c->stream>>>(p->args);
+// sum floats [off, off + n) of the mapped buffers over ranks, in place on every rank, as one kernel on `st` (captured into the
+// step graph like any kernel).  Two launches that may be in flight together on a GPU must use different signal sets (chan 0 / 1).
+int dg_dp_p2p_allreduce(dg_ctx *c, dg_p2p *p, cudaStream_t st, size_t off, size_t n, int chan) {
+    DG_REQUIRE(off % 4 == 0 && n % 4 == 0 && chan >= 0 && chan < 2, "peer exchange: bad range");
+    P2PArgs a = p->args;
+    a.off4 = off / 4; a.n4 = n / 4; a.chan = chan; a.tl = c->tl;
+    DG_CUDA(dg_launch_pdl(p2p_allreduce_kernel, dim3(DG_P2P_BLOCKS), dim3(512), 0, st, a));
     c->launches++;
-    DG_CUDA(cudaGetLastError());
     return 0;
 }

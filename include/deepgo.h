@@ -62,7 +62,7 @@ int dg_prof_get(dg_ctx *ctx, int kind, float *ms_total, long long *launches);
 /* Step timeline that also sees inside a replayed CUDA graph (process started with DG_TL=1): per kernel of the training step
  * {first CTA in, first CTA past its dependency wait, last CTA out} in globaltimer nanoseconds, in the order first conv, conv
  * chain, head, input-gradient chain, weight gradient (3x3 layers), weight gradient (first layer), gradient finalize, SGD, head
- * reduction, peer-memory gradient exchange; copies min(n, 30) values, then resets the stamps.  Profiling aid, no reference counterpart. */
+ * reduction, peer-memory gradient exchange (two launches); copies min(n, 33) values, then resets the stamps.  Profiling aid, no reference counterpart. */
 int dg_prof_timeline(dg_ctx *ctx, unsigned long long *out, int n);
 
 /* ---- data parallel (nn.DataParallelTable(1), experiments.lua:155-168) ---------------------- */

@@ -27,13 +27,13 @@ print("loss", loss, "launches", ctx.launch_count())
 if os.environ.get("DG_TL"):
     # in-graph timeline of the last step (globaltimer ns relative to the first kernel of the step)
     from deepgo_b200 import ffi, lib
-    names = ["conv0", "conv chain", "head", "dgrad chain", "wgrad 3x3", "wgrad first", "finalize", "sgd", "head reduce", "peer exchange"]
-    buf = ffi.new("unsigned long long[30]")
-    lib().dg_prof_timeline(ctx.h, buf, 30)          # drop the stamps of the steps so far
+    names = ["conv0", "conv chain", "head", "dgrad chain", "wgrad 3x3", "wgrad first", "finalize", "sgd", "head reduce", "peer exchange", "peer exch. 2"]
+    buf = ffi.new("unsigned long long[33]")
+    lib().dg_prof_timeline(ctx.h, buf, 33)          # drop the stamps of the steps so far
     m.encode_resident()
     m.train_step(0.01)
-    lib().dg_prof_timeline(ctx.h, buf, 30)
-    v = [int(buf[i]) for i in range(30)]
+    lib().dg_prof_timeline(ctx.h, buf, 33)
+    v = [int(buf[i]) for i in range(33)]
     t0 = min(x for i, x in enumerate(v) if i % 3 == 0 and x != 2**64 - 1)
     for k, nm in enumerate(names):
         a, g, e = v[3 * k:3 * k + 3]
