@@ -249,7 +249,7 @@ def run_ours(args, rank, local_rank, world):
         flops = F_CONV_LAYER * BATCH * layers_per_launch
         achieved = flops / (avg_ms * 1e-3) / 1e12
         roofline = {"kernel": "conv_umma_kernel (3x3, 128->128, forward, %g layers per launch)" % layers_per_launch, "bound": "tensor",
-                    "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained, "traffic": None,
+                    "achieved": achieved, "peak": sustained, "unit": "TFLOP/s", "frac": achieved / sustained, "traffic": ncu_traffic(),
                     "peak_source": peak_src + ", sustained bf16", "avg_launch_ms": avg_ms, "flops_per_launch": flops}
     whole = F_TRAIN * BATCH / (ms_per_step * 1e-3) / 1e12
 
@@ -275,6 +275,16 @@ def run_ours(args, rank, local_rank, world):
         "kernels": kern}))
     if dist is not None:
         dist.destroy_process_group()
+
+
+def ncu_traffic():
+    """DRAM bytes (read + write) of one launch of the roofline kernel, from the committed `ncu --set full` capture
+    (profiles/roofline_traffic_r1.json: a measured constant of the kernel, not re-measured by the bench)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic_r1.json")) as f:
+            return json.load(f)["dram_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def main():

@@ -474,7 +474,7 @@ static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
     m->fused_step = false;
     if (rc) return rc;
     if (int rc2 = dg_dp_finish(c)) return rc2;                             // buckets were issued layer by layer in backward
-    if (rate_from_device) return dg_bf16_sgd_step(m, rate, m->d_rate);
+    if (m->bf) return dg_bf16_sgd_step(m, rate, rate_from_device ? m->d_rate : nullptr);   // reads the accumulation buffers directly
     return dg_sgd_step(m, rate);                                           // train.lua:131
 }
 
