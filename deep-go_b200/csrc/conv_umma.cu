@@ -75,7 +75,7 @@ template <bool PAIR, int MODE>      // MODE 0: forward (bias + ReLU), 1: input g
 __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t w_full[CONV_MAX_STAGES], w_empty[CONV_MAX_STAGES], w_peer[CONV_MAX_STAGES];
-    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_peer, img_empty, acc_full, acc_ready;
+    __shared__ uint64_t img_full[CONV_MAX_KPANELS], img_peer, img_empty, acc_full, acc_ready, acc_ready01;
     __shared__ uint32_t tmem_base_s;
     __shared__ uint32_t row_s[4][256], mask_s[MODE == 1 ? 8 : 1][256];   // per-thread tables of the epilogue warps (see there)
 
@@ -92,6 +92,11 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
     const int nnb = p.cout / p.nb;
     const int chunks_kp = p.kp >> 3;
     // positions: one per CTA; a pair walks two neighbouring positions together (the second may not exist when n is odd)
+    // Chains with three accumulator tiles rotate them through the four 128-column TMEM blocks: tile t of the a-th layer lives in block
+    // (t + 3a) mod 4, so the NEXT layer's tile 0 owns a block that is free while this layer's tiles are still being drained.  Its MMAs
+    // need the output rows of tiles 0 and 1 only (21-row halo), so the warp issuing tile 0 starts as soon as those two are drained
+    // and runs up to the depth of the weight ring ahead -- under the drain of tile 2.
+    const bool rotate = !PAIR && p.ntiles == 3 && p.nchain > 1 && p.nb * 4 <= 512 && p.cout == p.nb;
     const int pos_first = PAIR ? 2 * (int)(blockIdx.x >> 1) : (int)blockIdx.x;
     const int pos_step = PAIR ? (int)(gridDim.x & ~1u) : (int)gridDim.x;
 
@@ -105,6 +110,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
         mbar_init(&img_empty, CONV_MMA_WARPS);    // every MMA-issuing warp commits its own MMAs
         mbar_init(&acc_full, CONV_MMA_WARPS);
         mbar_init(&acc_ready, PAIR ? 16 : 8);
+        mbar_init(&acc_ready01, 8);
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -215,7 +221,9 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
                     // the epilogue warps have drained the previous accumulators, written the previous layer's output rows
                     // into the shared-memory image (chains) and, in forward mode, pre-loaded the accumulators with the bias
-                    if (PAIR) mbar_wait_cluster(&acc_ready, a & 1); else mbar_wait(&acc_ready, a & 1);
+                    if (PAIR) mbar_wait_cluster(&acc_ready, a & 1);
+                    else if (rotate && mma_id == 0) mbar_wait(&acc_ready01, a & 1);      // tile 0 may start before tile 2 of the previous layer is drained
+                    else mbar_wait(&acc_ready, a & 1);
                     tc_fence_after();
                     if (lane == 0 && j == 0 && mma_id == 0) CHAIN_STAMP(l, 0);
                     uint32_t a_lo_k = a_lo_first;
@@ -235,7 +243,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                                 if (elect_one()) {
                                     for (int tile = mma_id; tile < p.ntiles; tile += CONV_MMA_WARPS) {
                                         uint32_t a_lo = a_lo_ky + kx + (uint32_t)tile * 128, b_lo = b_lo_s;
-                                        const uint32_t d_tmem = tmem_base + (uint32_t)tile * p.nb;
+                                        const uint32_t d_tmem = tmem_base + (rotate ? (uint32_t)((tile + 3 * a) & 3) : (uint32_t)tile) * p.nb;
 #pragma unroll 4
                                         for (int ks = 0; ks < ksteps; ++ks, a_lo += a_kstep, b_lo += b_kstep) {
                                             const uint32_t accumulate = first_stage ? (uint32_t)(ks != 0) : 1u;
@@ -329,6 +337,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                         tc_fence_before();
                         __syncwarp();
                         arrive_ready();
+                        if (rotate && lane == 0) mbar_arrive(&acc_ready01);
                     }
                     // backward: while the MMAs run, the ReLU mask of each item (stored input of the layer > 0) is compressed to one
                     // 32-bit word, laid out so that the drain expands it with byte permutes: element (chunk g, pair j, half h)
@@ -387,7 +396,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                                 row_of(tile, blk, l, rho, rho_out, rho_m, valid, c0);
                                 const int chunk0 = (nbk * p.nb + c0) >> 3;
                                 uint32_t r[32];
-                                tmem_ld32(tm_lane + tile * p.nb + c0, r);
+                                tmem_ld32(tm_lane + (rotate ? (uint32_t)((tile + 3 * a) & 3) : (uint32_t)tile) * p.nb + c0, r);
                                 const uint32_t mbits = MODE == 1 ? mask_s[item][et] : 0u;
                                 tmem_ld_wait();
                                 if (valid) {
@@ -425,6 +434,13 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                                 }
                                 if (MODE == 0 && item + CONV_BIAS_RING < items) { load_bias_item(ftile, fblk, l, nbk, bq[MODE == 0 ? u : 0]); advance(ftile, fblk); }
                                 advance(tile, blk);
+                                if (rotate && chain_more && tile == 2 && blk == 0) {
+                                    // tiles 0 and 1 are drained: the next layer's tile 0 has its input rows and a free accumulator block
+                                    fence_proxy_async();
+                                    tc_fence_before();
+                                    __syncwarp();
+                                    if (lane == 0) mbar_arrive(&acc_ready01);
+                                }
                             }
                         }
                     }
