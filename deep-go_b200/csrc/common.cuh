@@ -155,5 +155,7 @@ int dg_dp_finish(dg_ctx *ctx);
 #define DG_MAX_RANKS 8
 struct dg_p2p;
 int dg_dp_p2p_setup(dg_ctx *ctx, float *buf, size_t nfloats, dg_p2p **out);
-int dg_dp_p2p_allreduce(dg_ctx *ctx, dg_p2p *p, cudaStream_t st, size_t off_floats, size_t n_floats, int chan);
+int dg_dp_p2p_allreduce(dg_ctx *ctx, dg_p2p *p, cudaStream_t st, size_t off_floats, size_t n_floats, int chan, int scatter_only);
+int dg_dp_p2p_barrier(dg_ctx *ctx, dg_p2p *p, cudaStream_t st);
+void dg_dp_p2p_peers(const dg_p2p *p, const float **buf, int *world, size_t *per4);
 void dg_dp_p2p_destroy(dg_p2p *p);

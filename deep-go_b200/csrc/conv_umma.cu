@@ -1462,13 +1462,23 @@ struct SgdPackLayer {
     int g_pitch, g_pad, g_first; // geometry of the layer's dZ image
 };
 
+// data parallel: after the reduce-scatter over NVLink peer memory the summed gradient of slice r lives on rank r only; the SGD kernel
+// pulls what it needs from the owner (world <= 1: everything is local)
+struct SgdPeers { const float *base; const float *buf[DG_MAX_RANKS]; size_t n, per4; int world; };
+__device__ __forceinline__ const float *sgd_grad_ptr(const SgdPeers &P, const float *local) {
+    if (P.world <= 1) return local;
+    const size_t off = (size_t)(local - P.base);
+    if (off >= P.n) return local;                    // not in the exchanged allocation
+    const int owner = min((int)((off >> 2) / P.per4), P.world - 1);
+    return P.buf[owner] + off;
+}
 #ifndef SGD_CO_B
 #define SGD_CO_B 4
 #define SGD_NT 256
 #endif
 template <int CO_B, int NT>      // output channels per block, threads per block
 __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__restrict__ table, float rate, const float *__restrict__ rate_dev,
-                                                       int R_out, int pitch_out, int pad_out, int smem_row, unsigned long long *tl) {
+                                                       int R_out, int pitch_out, int pad_out, int smem_row, unsigned long long *tl, const __grid_constant__ SgdPeers peers) {
     extern __shared__ float wrow[];                 // [CO_B][smem_row]: the block's updated weight rows
     __shared__ float bnew[CO_B], bsum[CO_B];
     __shared__ float bpart[(CO_B * DG_POINTS + NT - 1) / NT][NT / 32][2];   // per-warp partial sums of the per-point bias gradient
@@ -1493,7 +1503,7 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
         for (int e = threadIdx.x; e < KK * cin4 * CO_B; e += NT) {
             const int r = e % CO_B, c4 = (e / CO_B) % cin4, t = e / (CO_B * cin4);
             if (r < nco) {
-                const float4 g = __ldg(g4 + ((size_t)t * cin4 + c4) * L.cout + co0 + r);
+                const float4 g = __ldcg(reinterpret_cast<const float4 *>(sgd_grad_ptr(peers, reinterpret_cast<const float *>(g4 + ((size_t)t * cin4 + c4) * L.cout + co0 + r))));
                 const float gj[4] = {g.x, g.y, g.z, g.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
@@ -1520,9 +1530,9 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
                 const int r = i / DG_POINTS, pt = i - r * DG_POINTS;
                 const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
                 const int rr = (x + L.g_pad) * L.g_pitch + y + L.g_pad - L.g_first;
-                ag[k] = __ldg(L.gab + ((size_t)(rr >> 2) * L.cout + co0 + r) * 4 + (rr & 3));
+                ag[k] = __ldcg(sgd_grad_ptr(peers, L.gab + ((size_t)(rr >> 2) * L.cout + co0 + r) * 4 + (rr & 3)));
             } else {
-                ag[k] = __ldg(L.ga + gi);
+                ag[k] = __ldcg(sgd_grad_ptr(peers, L.ga + gi));
             }
         }
         if (from_acc) {
@@ -1546,7 +1556,7 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
             if (i < total) {
                 wv[k] = Wp[i];
                 if (from_acc) { const int r = i / row; gv[k] = wrow[r * smem_row + (i - r * row)]; }
-                else gv[k] = __ldg(Gp + i);
+                else gv[k] = __ldcg(sgd_grad_ptr(peers, Gp + i));
             }
         }
 #pragma unroll
@@ -1574,7 +1584,7 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
         __syncthreads();
     }
     if (threadIdx.x < nco) {
-        const float v = fmaf(neg_rate, from_acc ? bsum[threadIdx.x] : L.gb[co0 + threadIdx.x], L.b[co0 + threadIdx.x]);
+        const float v = fmaf(neg_rate, from_acc ? bsum[threadIdx.x] : __ldcg(sgd_grad_ptr(peers, L.gb + co0 + threadIdx.x)), L.b[co0 + threadIdx.x]);
         L.b[co0 + threadIdx.x] = v;
         bnew[threadIdx.x] = v;
     }
@@ -1647,6 +1657,7 @@ struct Bf16Path {
     std::vector<SgdPackLayer> sgd_host;
     dg_p2p *p2p = nullptr;                 // data parallel: the peers' accumulation buffers mapped over NVLink (NULL: NCCL)
     bool p2p_tried = false;
+    bool p2p_pull = false;                 // the exchange is a reduce-scatter, the SGD kernel pulls each slice from its owner
     bool defer_grads = false;              // fused steps hand the conv gradients to the SGD kernel in the accumulation buffers
     bool grads_pending = false;            // the conv layers' gradient of the last fused step is still in gacc / gab, not in m->grads
     int sgd_smem_row = 0, sgd_max_co8 = 0;
@@ -1933,12 +1944,26 @@ int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev) {
     dg_ctx *c = m->ctx;
     {
         dg_prof_scope _ps(c, DG_K_SGD);
+        SgdPeers peers{};
+        if (b->grads_pending && b->p2p && b->p2p_pull) {
+            peers.base = b->gacc; peers.n = b->gacc_floats;
+            dg_dp_p2p_peers(b->p2p, peers.buf, &peers.world, &peers.per4);
+        }
         DG_CUDA(dg_launch_pdl(sgd_pack_kernel<SGD_CO_B, SGD_NT>, dim3(b->sgd_max_co8, m->L), dim3(SGD_NT), (size_t)SGD_CO_B * b->sgd_smem_row * 4, c->stream,
-                              (const SgdPackLayer *)(b->grads_pending ? b->sgd_table_acc : b->sgd_table), rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row, c->tl));
+                              (const SgdPackLayer *)(b->grads_pending ? b->sgd_table_acc : b->sgd_table), rate, rate_dev, (int)DG_R3, b->g3.pitch, b->g3.pad, b->sgd_smem_row, c->tl, peers));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
+}
+
+// pull mode: fetch every slice of the summed gradient from its owner into the local buffer (before the gradient vector is built from it)
+__global__ void __launch_bounds__(256) p2p_pull_all_kernel(const __grid_constant__ SgdPeers P, float *local) {
+    const size_t n4 = P.n >> 2;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float *src = sgd_grad_ptr(P, local + 4 * i);
+        if (src != local + 4 * i) reinterpret_cast<float4 *>(local)[i] = __ldcg(reinterpret_cast<const float4 *>(src));
+    }
 }
 
 // data parallel, first fused step (a collective: every rank gets here): map the peers' accumulation buffers.  Falls back to NCCL
@@ -1954,6 +1979,9 @@ int dg_bf16_dp_prepare(dg_model *m) {
         fprintf(stderr, "deepgo_b200: %s\n", dg_last_error());
         b->p2p = nullptr;
     }
+    // pull mode (DG_DP_PULL=1: reduce-scatter only, the SGD kernel fetches each slice from its owner) is implemented and tested but
+    // slower: remote reads inside the latency-bound SGD blocks cost 27 us, the write phase it saves 4 us (2 GPUs)
+    b->p2p_pull = b->p2p != nullptr && getenv("DG_DP_PULL") != nullptr;
     return 0;
 }
 
@@ -1963,6 +1991,15 @@ int dg_bf16_sync_grads(dg_model *m) {
     dg_ctx *c = m->ctx;
     if (!b->grads_pending) return 0;
     const LayerInfo &l0 = m->layers[0], &lh = m->layers[m->L - 1];
+    if (b->p2p && b->p2p_pull && c->world > 1) {
+        // the local buffer holds the summed values of this rank's slice only (the peers keep theirs until every rank has entered its
+        // next step, and this call is ordered before ours)
+        SgdPeers peers{};
+        peers.base = b->gacc; peers.n = b->gacc_floats;
+        dg_dp_p2p_peers(b->p2p, peers.buf, &peers.world, &peers.per4);
+        p2p_pull_all_kernel<<<2 * b->num_sms, 256, 0, c->stream>>>(peers, b->gacc);
+        c->launches++;
+    }
     DG_CUDA(cudaMemsetAsync(m->grads + l0.offW, 0, (lh.offW - l0.offW) * 4, c->stream));
     wgrad_finalize_kernel<<<dim3(96, m->L - 1), 256, FIN_SMEM_FLOATS * 4, c->stream>>>(b->fin_table, nullptr);
     c->launches++;
@@ -2087,6 +2124,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
     if (!b->deterministic) {
         DG_CUDA(cudaEventRecord(b->ev_fork, c->stream));
         DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_fork, 0));
+        // data parallel, pull mode: the peers' SGD kernels of the previous step read this buffer; every rank is past them once all
+        // ranks have reached this barrier (it is ordered after this rank's own SGD kernel)
+        if (m->fused_step && b->p2p && b->p2p_pull) if (int rc = dg_dp_p2p_barrier(c, b->p2p, b->side)) return rc;
         DG_CUDA(cudaMemsetAsync(b->gacc, 0, b->gacc_floats * 4, b->side));
         DG_CUDA(cudaEventRecord(b->ev_memset, b->side));
     }
@@ -2228,7 +2268,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         if (defer) {
             // head block + the conv layers not exchanged yet: one contiguous range from the start of the allocation
             const size_t end = dp_done_from < m->L - 1 ? b->gacc_off[dp_done_from] : b->gacc_floats;
-            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p, c->stream, 0, end, 1)) return rc; }   // one kernel over NVLink peer memory
+            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p, c->stream, 0, end, 0, b->p2p_pull ? 1 : 0)) return rc; }   // one kernel over NVLink peer memory
             else if (int rc = dg_dp_bucket(c, b->gacc, end)) return rc;
         } else {
             if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + head_n - l0.offW)) return rc;

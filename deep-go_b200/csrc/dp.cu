@@ -108,6 +108,7 @@ struct P2PArgs {
     int rank, world;
     size_t off4, n4;                         // float4 range of the buffer this launch exchanges
     int chan;                                // signal set: launches that may overlap on a GPU use different ones
+    int scatter_only;                        // 1: the sum of slice r stays on rank r (the consumer pulls it), 0: written to every rank
     unsigned long long *tl;                  // optional step timeline (DG_TL=1)
 };
 
@@ -165,12 +166,17 @@ __global__ void __launch_bounds__(512) p2p_allreduce_kernel(const __grid_constan
                 s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
                 if (two) { t.x += w[r].x; t.y += w[r].y; t.z += w[r].z; t.w += w[r].w; }
             }
+        if (a.scatter_only) {
+            p2p_st_v4(reinterpret_cast<float4 *>(a.buf[a.rank]) + i, s);
+            if (two) p2p_st_v4(reinterpret_cast<float4 *>(a.buf[a.rank]) + i2, t);
+        } else {
 #pragma unroll
-        for (int r = 0; r < DG_MAX_RANKS; ++r)
-            if (r < a.world) {
-                p2p_st_v4(reinterpret_cast<float4 *>(a.buf[r]) + i, s);
-                if (two) p2p_st_v4(reinterpret_cast<float4 *>(a.buf[r]) + i2, t);
-            }
+            for (int r = 0; r < DG_MAX_RANKS; ++r)
+                if (r < a.world) {
+                    p2p_st_v4(reinterpret_cast<float4 *>(a.buf[r]) + i, s);
+                    if (two) p2p_st_v4(reinterpret_cast<float4 *>(a.buf[r]) + i2, t);
+                }
+        }
     }
     // nobody leaves (and lets its next kernel read, or its next step clear, the buffer) before every rank has written every slice
     p2p_barrier(a, &P2PSignals::end, call);
@@ -238,7 +244,7 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
         dg_dp_p2p_destroy(p);
         DG_REQUIRE(false, "peer exchange: a rank could not map its peers' memory (CUDA IPC / P2P unavailable): using NCCL");
     }
-    p->args.rank = c->rank; p->args.world = c->world; p->args.off4 = 0; p->args.n4 = nfloats / 4; p->args.chan = 0;
+    p->args.rank = c->rank; p->args.world = c->world; p->args.off4 = 0; p->args.n4 = nfloats / 4; p->args.chan = 0; p->args.scatter_only = 0;
     *out = p;
     return 0;
 }
@@ -252,11 +258,33 @@ void dg_dp_p2p_destroy(dg_p2p *p) {
 
 // sum floats [off, off + n) of the mapped buffers over ranks, in place on every rank, as one kernel on `st` (captured into the
 // step graph like any kernel).  Two launches that may be in flight together on a GPU must use different signal sets (chan 0 / 1).
-int dg_dp_p2p_allreduce(dg_ctx *c, dg_p2p *p, cudaStream_t st, size_t off, size_t n, int chan) {
+int dg_dp_p2p_allreduce(dg_ctx *c, dg_p2p *p, cudaStream_t st, size_t off, size_t n, int chan, int scatter_only) {
     DG_REQUIRE(off % 4 == 0 && n % 4 == 0 && chan >= 0 && chan < 2, "peer exchange: bad range");
     P2PArgs a = p->args;
-    a.off4 = off / 4; a.n4 = n / 4; a.chan = chan; a.tl = c->tl;
+    a.off4 = off / 4; a.n4 = n / 4; a.chan = chan; a.tl = c->tl; a.scatter_only = scatter_only;
     DG_CUDA(dg_launch_pdl(p2p_allreduce_kernel, dim3(DG_P2P_BLOCKS), dim3(512), 0, st, a));
     c->launches++;
     return 0;
+}
+
+// every rank has reached this point of `st` (one block, signal set 1): used before a rank clears a buffer its peers may still be reading
+__global__ void __launch_bounds__(32) p2p_barrier_kernel(const __grid_constant__ P2PArgs a) {
+    __shared__ unsigned int call_s;
+    if (threadIdx.x == 0) call_s = ++(a.sig[a.rank] + a.chan)->calls[0];
+    __syncthreads();
+    p2p_barrier(a, &P2PSignals::begin, call_s);
+}
+int dg_dp_p2p_barrier(dg_ctx *c, dg_p2p *p, cudaStream_t st) {
+    P2PArgs a = p->args;
+    a.chan = 1;
+    p2p_barrier_kernel<<<1, 32, 0, st>>>(a);
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
+}
+// the mapping, for kernels that pull a summed slice from its owner: buf[r] = rank r's buffer as mapped here, per4 = float4 per slice
+void dg_dp_p2p_peers(const dg_p2p *p, const float **buf, int *world, size_t *per4) {
+    for (int r = 0; r < DG_MAX_RANKS; ++r) buf[r] = r < p->args.world ? p->args.buf[r] : nullptr;
+    *world = p->args.world;
+    *per4 = (p->args.n4 + p->args.world - 1) / p->args.world;
 }

@@ -1,5 +1,6 @@
 """-m gpu, needs >= 2 GPUs (skipped otherwise): two ranks, one per GPU, train on the two halves of a batch through
-the library's bucketed NCCL allreduce and must end with the parameters of one rank training on the whole batch."""
+the library's gradient exchange (NVLink peer memory for the bf16 path, NCCL for fp32) and must end with the parameters
+of one rank training on the whole batch; the gradient vector read back after a step must be the same on both ranks."""
 import os
 import socket
 import subprocess
@@ -32,6 +33,7 @@ for _ in range(3):
     m.set_batch_raw(mine["raw"], mine["player"], mine["rank"], None, mine["x"], mine["y"])
     m.train_step(0.05)
 np.save(os.environ["DG_OUT"] + ".%d.npy" % rank, m.get_params())
+np.save(os.environ["DG_OUT"] + ".g%d.npy" % rank, m.get_grads())
 dist.barrier()
 dist.destroy_process_group()
 '''
@@ -63,5 +65,7 @@ def test_two_gpus_match_one(tmp_path, prec):
                            "--master-port", str(port), str(script)], env=env, timeout=300)
     a = np.load(str(tmp_path / "out") + ".0.npy"); b = np.load(str(tmp_path / "out") + ".1.npy")
     assert np.array_equal(a, b)                          # replicas stay identical
+    ga = np.load(str(tmp_path / "out") + ".g0.npy"); gb = np.load(str(tmp_path / "out") + ".g1.npy")
+    assert np.array_equal(ga, gb) and np.abs(ga).max() > 0  # the summed gradient of the last step, materialised on demand
     tol = 1e-5 if prec == 0 else 2e-3
     assert np.abs(a - ref).max() < tol
