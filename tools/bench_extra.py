@@ -59,6 +59,45 @@ sgd_ms = ps["sgd"][0] / ps["sgd"][1]
 out["sgd"] = {"params": m2.P, "ms": sgd_ms, "algorithmic_bytes": 12 * m2.P, "GBps": 12 * m2.P / (sgd_ms * 1e-3) / 1e9,
               "frac_of_hbm_peak": 12 * m2.P / (sgd_ms * 1e-3) / 1e9 / HBM, "note": "8.4 MB vectors: L2-resident, launch-latency dominated"}
 
+
+# ---- c3: the paper's largest net, 12 x 192, batch 256: bf16 training throughput + bf16-vs-fp32 agreement -----------------
+def he_params_lc(seed, L, C):
+    rng = np.random.default_rng(seed)
+    chans = [37] + [C] * (L - 1) + [1]
+    ks = [5] + [3] * (L - 1)
+    parts = []
+    for i in range(L):
+        fan = chans[i] * ks[i] * ks[i]
+        parts += [rng.normal(0, np.sqrt(2.0 / fan), chans[i + 1] * fan), rng.normal(0, 0.05, chans[i + 1]), rng.normal(0, 0.05, chans[i + 1] * 361)]
+    parts[-2] = parts[-2] + 1.0          # lift the last layer's bias so the final ReLU is not dead at init
+    return np.concatenate(parts).astype(np.float32)
+
+
+B3, L3, C3 = 256, 12, 192
+p3 = he_params_lc(3, L3, C3)
+b3 = bench.synthetic_batch(33, B3)
+m3 = engine.Model(ctx, L3, C3, engine.DG_PREC_BF16, max_batch=B3)
+m3.set_params(p3)
+m3.set_batch_raw(b3["raw"], b3["player"], b3["rank"], b3["sym"], b3["x"], b3["y"])
+lp_bf = m3.forward()
+for _ in range(3):
+    m3.encode_resident(); m3.train_step(0.0, want_loss=False)
+ctx.synchronize()
+ctx.timer_start()
+for _ in range(10):
+    m3.encode_resident(); m3.train_step(0.0, want_loss=False)
+ms3 = ctx.timer_stop() / 10
+F3 = 3 * (2 * 361 * (25 * 37 * C3 + 10 * 9 * C3 * C3 + 9 * C3)) - 2 * 361 * 25 * 37 * C3
+m3f = engine.Model(ctx, L3, C3, engine.DG_PREC_FP32, max_batch=B3)
+m3f.set_params(p3)
+m3f.set_batch_raw(b3["raw"], b3["player"], b3["rank"], b3["sym"], b3["x"], b3["y"])
+lp_f = m3f.forward()
+out["c3_12x192_batch256"] = {"batch": B3, "ms_per_step": ms3, "positions_per_s": B3 / (ms3 * 1e-3), "tflops_algorithmic": B3 * F3 / (ms3 * 1e-3) / 1e12,
+                             "bf16_vs_fp32_logprob_max_abs": float(np.abs(lp_bf - lp_f).max()),
+                             "bf16_vs_fp32_top1_agreement": float((lp_bf.argmax(1) == lp_f.argmax(1)).mean()),
+                             "note": "bf16 tensor-core path (per-layer launches: 192 channels need two N blocks) vs the fp32 CUDA-core path of this library, He init, rate 0"}
+del m3, m3f
+
 # ---- board analysis --------------------------------------------------------------------------------------------
 g = np.load(os.path.join(bench.ROOT, "tests", "golden", "positions.npz"))
 stones = np.ascontiguousarray(np.tile(g["raw"][:, 0], (4, 1, 1)))          # 17,592 boards
