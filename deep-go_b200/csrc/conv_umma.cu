@@ -491,8 +491,9 @@ struct WgradParams {
     long long *dbg;       // optional timeline (DG_TIMELINE=1): per CTA {start, mma-loop start, mma-loop end, total wait, end}
 };
 
-#define WG_RP 128         // K rows per stage
+#define WG_RP_MAX 128     // K rows per stage: a template parameter (96 for the 3x3 geometry: four 50 KB stages instead of three 65 KB ones)
 
+template <int WG_RP>
 __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     // accumulator hand-over is per MMA warp (= per group of kernel columns): the drain of warp w's columns overlaps the other
@@ -1751,7 +1752,7 @@ static int launch_conv(dg_model *m, ConvParams cp) {
     return 0;
 }
 
-struct WgradPlan { int nb, n_mblk, n_nblk, combos, splits, nstages; size_t smem, scratch_bytes; };
+struct WgradPlan { int nb, n_mblk, n_nblk, combos, splits, nstages, rp; size_t smem, scratch_bytes; };
 
 static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const Geom &g, WgradPlan &w) {
     w.nb = cin_pad;
@@ -1762,6 +1763,11 @@ static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const
     w.combos = ksize * w.n_mblk * w.n_nblk;
     DG_REQUIRE(w.combos <= m->bf->num_sms, "bf16 path: too many weight-gradient tiles");
     // a multiple of the panels per position: every CTA then sees one panel index only (its bias-gradient accumulator is one panel)
+    // K rows per ring stage.  96 (four 50 KB stages instead of three 65 KB ones, DG_WG_RP96=1) was measured: no gain, the producer
+    // then issues a third more copies per byte and the units no longer divide evenly among the CTAs
+    static const bool rp96 = getenv("DG_WG_RP96") != nullptr;
+    w.rp = (g.ntiles * 128) % 96 == 0 && rp96 ? 96 : 128;
+    const int WG_RP = w.rp;
     const int panels = g.ntiles * 128 / WG_RP;
     w.splits = m->bf->num_sms / w.combos;
     if (w.splits > panels) w.splits -= w.splits % panels;
@@ -1869,7 +1875,7 @@ int dg_bf16_create(dg_model *m) {
         const Geom &gl = l == 0 ? b->g_first : b->g3;
         WgradPlan wpl;
         if (int rc = wgrad_plan(m, b->ops[l].cin_pad, m->layers[l].cout, m->layers[l].k, gl, wpl)) return rc;
-        if (m->layers[l].k * wpl.nb + WG_RP > 512 || wpl.splits % (gl.ntiles * 128 / WG_RP) != 0) b->fused_bias = false;
+        if (m->layers[l].k * wpl.nb + wpl.rp > 512 || wpl.splits % (gl.ntiles * 128 / wpl.rp) != 0) b->fused_bias = false;
         b->gacc_off[l] = b->gacc_floats; b->gacc_floats += (size_t)m->layers[l].k * m->layers[l].k * b->ops[l].cin_pad * m->layers[l].cout;
         b->gab_off[l] = b->gacc_floats; b->gacc_floats += (size_t)gl.ntiles * 128 * m->layers[l].cout;
     }
@@ -1900,7 +1906,8 @@ int dg_bf16_create(dg_model *m) {
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
-    DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+    DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+    DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
     DG_CUDA(cudaFuncSetAttribute(head_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 4096));
     DG_CUDA(cudaFuncSetAttribute(head_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 8192));
     return 0;
@@ -2208,7 +2215,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
         wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
         // two layer groups when the layers and the splits divide evenly (the per-CTA panel index must stay fixed for the bias gradient)
-        const int panels_l = g.ntiles * 128 / WG_RP;
+        const int panels_l = g.ntiles * 128 / w.rp;
         const int ngroups = (!b->deterministic && nl % 2 == 0 && w.splits % (2 * panels_l) == 0 && m->n * panels_l >= w.splits) ? 2 : 1;
         wp.ngroups = ngroups;
         wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits / ngroups; wp.nstages = w.nstages;
@@ -2217,7 +2224,8 @@ int dg_bf16_backward(dg_model *m, float scale) {
         // deterministic path: this scratch half was last read by the reduction two layers ago
         if (b->deterministic && rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
         { dg_prof_scope _ps(c, DG_K_WGRAD);
-        DG_CUDA(dg_launch_pdl(wgrad_umma_kernel, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp));
+        if (w.rp == 96) DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<96>, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp));
+        else DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<128>, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp));
         }
         c->launches++;
         if (wp.dbg) {
