@@ -564,11 +564,16 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                     uint8_t *sa = smem + (size_t)s * stage_bytes, *sb = sa + a_bytes;
                     const int row0 = p.first + panel * WG_RP;
                     const uint8_t *asrc = (const uint8_t *)p.dz[li] + (((size_t)pos * chunks_dz + mblk * 16) * p.R + row0) * 16;
-                    for (int c = 0; c < a_chunks; ++c, asrc += (size_t)p.R * 16)
-                        bulk_g2s(sa + (size_t)c * WG_RP * 16, asrc, WG_RP * 16, &s_full[s]);
+                    // (unrolled: each copy needs its operands moved to uniform registers, a dependent ~40-cycle chain per copy otherwise)
+                    const uint32_t sa_u = smem_u32(sa), sb_u = smem_u32(sb), bar_u = smem_u32(&s_full[s]);
+                    const size_t src_stride = (size_t)p.R * 16;
+#pragma unroll 8
+                    for (int c = 0; c < a_chunks; ++c)
+                        bulk_g2s_u(sa_u + (uint32_t)c * WG_RP * 16, asrc + (size_t)c * src_stride, WG_RP * 16, bar_u);
                     const uint8_t *bsrc = (const uint8_t *)p.x[li] + (((size_t)pos * chunks_x + nblk * (p.nb >> 3)) * p.R + row0 + brow_off) * 16;
-                    for (int c = 0; c < (p.nb >> 3); ++c, bsrc += (size_t)p.R * 16)
-                        bulk_g2s(sb + (size_t)c * rb_pad * 16, bsrc, (uint32_t)rb * 16, &s_full[s]);
+#pragma unroll 8
+                    for (int c = 0; c < (p.nb >> 3); ++c)
+                        bulk_g2s_u(sb_u + (uint32_t)c * rb_pad * 16, bsrc + (size_t)c * src_stride, (uint32_t)rb * 16, bar_u);
                 }
                 __syncwarp();
                 if (p.dbg) { const long long t2 = clock64(); pw += t1 - t0; pi += t2 - t1; }

@@ -59,6 +59,12 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src, uint32
                  : "memory");
 }
 
+// same with the shared-memory addresses already converted (loops that issue many copies)
+__device__ __forceinline__ void bulk_g2s_u(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
 // pull `bytes` (multiple of 16) at src into L2 ahead of a later bulk copy
 __device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
