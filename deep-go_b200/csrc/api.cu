@@ -493,7 +493,8 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
         // the ~50 launches and the cross-stream event edges of a step are captured once per batch size and replayed
         *m->h_rate = rate;
         DG_CUDA(cudaMemcpyAsync(m->d_rate, m->h_rate, 4, cudaMemcpyHostToDevice, c->stream));
-        if (!m->step_graph || m->step_graph_n != m->n) {
+        const int in_mode = dg_bf16_input_mode(m);
+        if (!m->step_graph || m->step_graph_n != m->n || m->step_graph_mode != in_mode) {
             if (m->step_graph) { cudaGraphExecDestroy(m->step_graph); m->step_graph = nullptr; }
             const long long l0 = c->launches;
             cudaGraph_t graph = nullptr;
@@ -507,6 +508,7 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
             cudaGraphDestroy(graph);
             DG_REQUIRE(e == cudaSuccess, "dg_train_step: cudaGraphInstantiate failed: %s", cudaGetErrorString(e));
             m->step_graph_n = m->n;
+            m->step_graph_mode = in_mode;
             m->step_graph_launches = c->launches - l0;
             c->launches = l0;
         }

@@ -49,6 +49,10 @@ struct ConvParams {
     int nchain;
     int n, cin, cout;
     unsigned long long *tl; int tl_id;
+    // first layer fed from raw records: the MMA warps build the input image in shared memory themselves (and store it to enc_out for
+    // the weight gradient) instead of waiting for a bulk copy of an image a separate encode kernel wrote
+    const uint8_t *enc_raw, *enc_player, *enc_rank, *enc_sym;
+    bf16 *enc_out;
     int R_in, pitch_in, pad_in, ksize, first, ntiles;
     int R_out, pitch_out, pad_out;     // geometry of the LAST layer's HBM output (intermediate layers: same as the input)
     int R_mask, pitch_mask, pad_mask;
@@ -58,6 +62,45 @@ struct ConvParams {
     int mode;
     long long *dbg;       // optional per-CTA phase timestamps (DG_TIMELINE=1), 8 slots per CTA
 };
+
+__device__ __forceinline__ int dg_src_point_d(int p, int sym) {
+    int x = p / DG_BOARD, y = p - x * DG_BOARD;
+    if (sym & 2) x = DG_BOARD - 1 - x;
+    if (sym & 4) y = DG_BOARD - 1 - y;
+    if (sym & 1) { int t = x; x = y; y = t; }
+    return x * DG_BOARD + y;
+}
+
+// preprocess() of one point (dataloader.lua:50-92): the 37 one-hot planes (+ zero padding to 48) as a bit mask, plane i = bit i
+__device__ __forceinline__ unsigned long long dg_plane_bits(const uint8_t *__restrict__ rec, int src, int pl, int rk) {
+    const int stone = rec[src], lib = rec[DG_POINTS + src], la = rec[(2 + pl - 1) * DG_POINTS + src];
+    const int kills = rec[(4 + pl - 1) * DG_POINTS + src], age = rec[6 * DG_POINTS + src], ladder = rec[(7 + pl - 1) * DG_POINTS + src];
+    unsigned long long m = 0;
+    m |= (unsigned long long)(stone == 0) << 0;
+    m |= (unsigned long long)(stone == pl) << 1;
+    m |= (unsigned long long)(stone == 3 - pl) << 2;
+    if (lib >= 1 && lib <= 3) m |= 1ull << (3 + lib - 1);
+    m |= (unsigned long long)(lib >= 4) << 6;
+    m |= (unsigned long long)(stone == 0 && la == 0) << 7;
+    if (la >= 1 && la <= 5) m |= 1ull << (7 + la);
+    m |= (unsigned long long)(la >= 6) << 13;
+    if (kills >= 1 && kills <= 6) m |= 1ull << (14 + kills - 1);
+    m |= (unsigned long long)(kills >= 7) << 20;
+    if (age >= 1 && age <= 5) m |= 1ull << (21 + age - 1);
+    m |= (unsigned long long)(ladder >= 1) << 26;
+    m |= 1ull << (27 + rk);
+    return m;
+}
+// 8 planes of that mask as 8 bf16 (1.0 = 0x3F80)
+__device__ __forceinline__ uint4 dg_plane_chunk(unsigned long long m, int c) {
+    const uint32_t bits = (uint32_t)(m >> (c * 8)) & 0xFFu;
+    uint4 o;
+    o.x = ((bits & 1) ? 0x3F80u : 0u) | ((bits & 2) ? 0x3F800000u : 0u);
+    o.y = ((bits & 4) ? 0x3F80u : 0u) | ((bits & 8) ? 0x3F800000u : 0u);
+    o.z = ((bits & 16) ? 0x3F80u : 0u) | ((bits & 32) ? 0x3F800000u : 0u);
+    o.w = ((bits & 64) ? 0x3F80u : 0u) | ((bits & 128) ? 0x3F800000u : 0u);
+    return o;
+}
 
 #define DBG_STAMP(slot) do { if (p.dbg) p.dbg[blockIdx.x * 8 + (slot)] = clock64(); } while (0)
 __device__ __forceinline__ long long dg_globaltimer() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
@@ -135,7 +178,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
         for (int pb = pos_first; pb < p.n; pb += pos_step, ++j) {
             const int pos = pb + (int)rank;
             mbar_wait(&img_empty, (j & 1) ^ 1);
-            if (pos < p.n && elect_one()) {
+            if (pos < p.n && !p.enc_raw && elect_one()) {
                 const uint8_t *src = (const uint8_t *)p.in + (size_t)pos * img_bytes;
                 for (int k = 0; k < nkp; ++k) {
                     mbar_arrive_expect_tx(&img_full[k], panel_bytes);
@@ -217,6 +260,39 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
             tc_fence_after();
         };
         for (int pb = pos_first; pb < p.n; pb += pos_step, ++j) {
+            if (!PAIR && p.enc_raw) {
+                // on-device encode fused into the first layer: these 96 threads turn the raw record of the position into the blocked bf16
+                // image (dataloader.lua:50-92 preprocess + the symmetry of transform()), in shared memory and in HBM
+                const int tix = mma_id * 32 + lane;
+                mbar_wait(&img_empty, (j & 1) ^ 1);                          // the previous position's MMAs no longer read the image
+                const uint8_t *rec = p.enc_raw + (size_t)pb * DG_RAW_PLANES * DG_POINTS;
+                const int pl = p.enc_player[pb], rk = p.enc_rank[pb], sy = p.enc_sym ? p.enc_sym[pb] : 0;
+                unsigned long long pm[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {                                // all loads first: 4 points x 6 bytes in flight
+                    const int pt = tix + 96 * k;
+                    pm[k] = pt < DG_POINTS ? dg_plane_bits(rec, dg_src_point_d(pt, sy), pl, rk) : 0ull;
+                }
+                const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+                for (uint32_t i = tix; i < img_bytes / 16; i += 96) *reinterpret_cast<uint4 *>(img + (size_t)i * 16) = z4;   // pads stay zero
+                asm volatile("bar.sync 1, 96;" ::: "memory");
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int pt = tix + 96 * k;
+                    if (pt < DG_POINTS) {
+                        const int x = pt / DG_BOARD, y = pt - x * DG_BOARD;
+                        const int rho = (x + p.pad_in) * p.pitch_in + y + p.pad_in;
+#pragma unroll
+                        for (int c = 0; c < 6; ++c) {
+                            const uint4 o = dg_plane_chunk(pm[k], c);
+                            *reinterpret_cast<uint4 *>(img + ((size_t)c * p.R_in + rho) * 16) = o;
+                            *reinterpret_cast<uint4 *>(p.enc_out + (((size_t)pb * 6 + c) * p.R_in + rho) * 8) = o;
+                        }
+                    }
+                }
+                fence_proxy_async();                                         // generic-proxy st.shared -> visible to the tensor core's async proxy
+                asm volatile("bar.sync 1, 96;" ::: "memory");
+            }
             for (int l = 0; l < p.nchain; ++l)
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
                     // the epilogue warps have drained the previous accumulators, written the previous layer's output rows
@@ -228,7 +304,7 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
                     if (lane == 0 && j == 0 && mma_id == 0) CHAIN_STAMP(l, 0);
                     uint32_t a_lo_k = a_lo_first;
                     for (int k = 0; k < nkp; ++k, a_lo_k += a_panel) {
-                        if (l == 0 && nbk == 0) {
+                        if (l == 0 && nbk == 0 && !(!PAIR && p.enc_raw)) {
                             mbar_wait(&img_full[k], j & 1);
                             if (PAIR && k == 0) mbar_wait_cluster(&img_peer, j & 1);
                             if (j == 0 && lane == 0 && mma_id == 0) DBG_STAMP(2 + (k > 0));
@@ -1340,13 +1416,6 @@ __global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__re
 // ---------------------------------------------------------------------------------------------
 // staging + parameter packing
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ int dg_src_point_d(int p, int sym) {
-    int x = p / DG_BOARD, y = p - x * DG_BOARD;
-    if (sym & 2) x = DG_BOARD - 1 - x;
-    if (sym & 4) y = DG_BOARD - 1 - y;
-    if (sym & 1) { int t = x; x = y; y = t; }
-    return x * DG_BOARD + y;
-}
 
 // raw records -> blocked bf16 input image [n][48/8][R][8] (planes 37..47 stay zero); same plane
 // definitions as encode.cu (dataloader.lua:50-92)
@@ -1360,33 +1429,12 @@ __global__ void __launch_bounds__(384) encode_blocked_kernel(const uint8_t *__re
     const int src = dg_src_point_d(p, sym ? sym[n] : 0);
     const uint8_t *rec = raw + (size_t)n * DG_RAW_PLANES * DG_POINTS;
     const int pl = player[n], rk = rank[n];
-    const int stone = rec[src], lib = rec[DG_POINTS + src], la = rec[(2 + pl - 1) * DG_POINTS + src];
-    const int kills = rec[(4 + pl - 1) * DG_POINTS + src], age = rec[6 * DG_POINTS + src], ladder = rec[(7 + pl - 1) * DG_POINTS + src];
-    unsigned long long m = 0;
-    m |= (unsigned long long)(stone == 0) << 0;
-    m |= (unsigned long long)(stone == pl) << 1;
-    m |= (unsigned long long)(stone == 3 - pl) << 2;
-    if (lib >= 1 && lib <= 3) m |= 1ull << (3 + lib - 1);
-    m |= (unsigned long long)(lib >= 4) << 6;
-    m |= (unsigned long long)(stone == 0 && la == 0) << 7;
-    if (la >= 1 && la <= 5) m |= 1ull << (7 + la);
-    m |= (unsigned long long)(la >= 6) << 13;
-    if (kills >= 1 && kills <= 6) m |= 1ull << (14 + kills - 1);
-    m |= (unsigned long long)(kills >= 7) << 20;
-    if (age >= 1 && age <= 5) m |= 1ull << (21 + age - 1);
-    m |= (unsigned long long)(ladder >= 1) << 26;
-    m |= 1ull << (27 + rk);
+    const unsigned long long m = dg_plane_bits(rec, src, pl, rk);
     const int x = p / DG_BOARD, y = p - x * DG_BOARD;
     const int rho = (x + pad) * pitch + y + pad;
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
-        const uint32_t bits = (uint32_t)(m >> (c * 8)) & 0xFFu;
-        uint4 o;
-        // bf16 1.0 = 0x3F80
-        o.x = ((bits & 1) ? 0x3F80u : 0u) | ((bits & 2) ? 0x3F800000u : 0u);
-        o.y = ((bits & 4) ? 0x3F80u : 0u) | ((bits & 8) ? 0x3F800000u : 0u);
-        o.z = ((bits & 16) ? 0x3F80u : 0u) | ((bits & 32) ? 0x3F800000u : 0u);
-        o.w = ((bits & 64) ? 0x3F80u : 0u) | ((bits & 128) ? 0x3F800000u : 0u);
+        const uint4 o = dg_plane_chunk(m, c);
         *reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8) = o;
     }
 }
@@ -1662,6 +1710,7 @@ struct Bf16Path {
     SgdPackLayer *sgd_table_acc = nullptr; // same, conv layers reading the accumulation buffers (fused step)
     std::vector<SgdPackLayer> sgd_host;
     dg_p2p *p2p = nullptr;                 // data parallel: the peers' accumulation buffers mapped over NVLink (NULL: NCCL)
+    bool x0_from_raw = false;              // the staged batch is raw records: the first conv layer encodes them itself (fused encode)
     bool p2p_tried = false;
     bool p2p_pull = false;                 // the exchange is a reduce-scatter, the SGD kernel pulls each slice from its owner
     bool defer_grads = false;              // fused steps hand the conv gradients to the SGD kernel in the accumulation buffers
@@ -2022,12 +2071,18 @@ int dg_bf16_sync_grads(dg_model *m) {
 }
 void dg_bf16_drop_pending_grads(dg_model *m) { m->bf->grads_pending = false; }
 // a replayed step graph runs no host code of dg_bf16_backward: restore what the captured step leaves behind
-void dg_bf16_after_fused_step(dg_model *m) { m->bf->grads_pending = m->bf->defer_grads; }
+void dg_bf16_after_fused_step(dg_model *m) { m->bf->grads_pending = m->bf->defer_grads; m->bf->x0_from_raw = false; }
 bool dg_bf16_defers_grads(const dg_model *m) { return m->bf->defer_grads; }
 
 int dg_bf16_stage_raw(dg_model *m) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
+    // DG_FUSED_ENCODE=1: the records stay as they are and the first conv kernel of the next forward pass encodes them.  Implemented and
+    // tested, but not faster: the separate 7 us encode kernel runs under the launch latency of the step graph, while the in-kernel encode
+    // adds 2.3 us to the first conv layer
+    static const bool fused = getenv("DG_FUSED_ENCODE") != nullptr;
+    if (fused && b->ops[0].cin_pad == 48) { b->x0_from_raw = true; return 0; }
+    b->x0_from_raw = false;
     { dg_prof_scope _ps(c, DG_K_ENCODE);
     DG_CUDA(dg_launch_pdl(encode_blocked_kernel, dim3(m->n), dim3(384), 0, c->stream, (const uint8_t *)m->d_raw, (const uint8_t *)m->d_player, (const uint8_t *)m->d_rank, (const uint8_t *)m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad));
     }
@@ -2035,9 +2090,12 @@ int dg_bf16_stage_raw(dg_model *m) {
     DG_CUDA(cudaGetLastError());
     return 0;
 }
+// 1: the next forward pass starts from raw records (fused encode), 0: from the blocked image in HBM -- two different step graphs
+int dg_bf16_input_mode(const dg_model *m) { return m->bf->x0_from_raw ? 1 : 0; }
 
 int dg_bf16_stage_planes(dg_model *m) {
     Bf16Path *b = m->bf;
+    b->x0_from_raw = false;
     dg_ctx *c = m->ctx;
     { dg_prof_scope _ps(c, DG_K_ENCODE);
     planes_to_blocked_kernel<<<m->n, 384, 0, c->stream>>>(m->act[0], b->x0, m->in_planes, b->g_first.rows, b->g_first.pitch, b->g_first.pad);
@@ -2119,10 +2177,14 @@ int dg_bf16_forward(dg_model *m) {
             cp.w[j] = b->ops[l + j].wf; cp.bias[j] = b->ops[l + j].ab; cp.mask[j] = nullptr; cp.out[j] = b->h[l + j + 1];
         }
         cp.nchain = nchain;
+        if (l == 0 && b->x0_from_raw) {
+            cp.enc_raw = m->d_raw; cp.enc_player = m->d_player; cp.enc_rank = m->d_rank; cp.enc_sym = m->d_sym; cp.enc_out = b->x0;
+        }
         if (int rc = conv_cfg(m, cp, b->ops[l].cin_pad, m->layers[l].cout)) return rc;
         if (int rc = launch_conv(m, cp)) return rc;
         l += nchain;
     }
+    b->x0_from_raw = false;               // the image is in HBM now: a second forward pass over the same batch loads it
     b->head_bwd_done = false;
     if (m->fused_step) return 0;          // dg_train_step: the head runs once, in dg_bf16_backward
     return launch_head(m, false, 0.f);

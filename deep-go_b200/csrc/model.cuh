@@ -22,6 +22,7 @@ struct dg_model {
     // captured CUDA graph of one fused training step (bf16 path, single GPU)
     cudaGraphExec_t step_graph = nullptr;
     int step_graph_n = 0;
+    int step_graph_mode = 0;           // input mode the graph was captured in (raw records vs blocked image)
     long long step_graph_launches = 0;
     float *d_rate = nullptr, *h_rate = nullptr;     // rate for the graph's SGD node (device scalar, pinned staging)
     // fp32 path (NCHW)
@@ -37,7 +38,8 @@ void dg_bf16_destroy(dg_model *m);
 int dg_bf16_params_changed(dg_model *m);
 int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev);   // fused SGD update + operand repack                 // refresh bf16 operand copies from the fp32 master
 int dg_bf16_stage_planes(dg_model *m);                   // act[0] (fp32 NCHW) -> blocked bf16 input image
-int dg_bf16_stage_raw(dg_model *m);                      // raw records -> blocked bf16 input image
+int dg_bf16_stage_raw(dg_model *m);                      // raw records -> blocked bf16 input image (deferred into the first conv kernel)
+int dg_bf16_input_mode(const dg_model *m);               // 1: the next forward pass encodes raw records itself
 int dg_bf16_forward(dg_model *m);                        // fills m->d_logp-ready logits via head
 int dg_bf16_backward(dg_model *m, float scale);
 int dg_bf16_dp_prepare(dg_model *m);                     // data parallel: map the peers' gradient buffers before the first fused step
