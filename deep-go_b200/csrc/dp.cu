@@ -105,6 +105,7 @@ struct P2PSignals {                          // lives in every rank's IPC-shared
 struct P2PArgs {
     float *buf[DG_MAX_RANKS];                // every rank's accumulation buffer as mapped HERE (buf[rank] is the local one)
     P2PSignals *sig[DG_MAX_RANKS];           // [2] signal sets per rank
+    float *stage[DG_MAX_RANKS];              // every rank's staging area [world][per4] float4: contributions pushed by the peers
     int rank, world;
     size_t off4, n4;                         // float4 range of the buffer this launch exchanges
     int chan;                                // signal set: launches that may overlap on a GPU use different ones
@@ -183,11 +184,65 @@ __global__ void __launch_bounds__(512) p2p_allreduce_kernel(const __grid_constan
     DG_TL_OUT(a.tl, DG_TL_P2P + a.chan);
 }
 
+// Push variant (DG_DP_WRITE=1; measured SLOWER on 2 GPUs: 50 us against 31 us -- 4.35 MB of remote writes take 20 us, no faster
+// than the remote reads of the kernel above, and there are two data phases instead of one): remote writes only.
+//   1. every rank pushes its contribution to slice o into rank o's staging area, for all o != rank.  No waiting: the staging areas
+//      were consumed before the previous call's closing barrier, and a skewed peer's weight-gradient kernels are not disturbed;
+//   2. barrier (all pushes have landed);  3. rank r sums slice r -- its own values and the staged ones, in rank order, all local
+//      reads -- and writes the sum into every rank's buffer;  4. barrier.
+__global__ void __launch_bounds__(512) p2p_push_allreduce_kernel(const __grid_constant__ P2PArgs a) {
+    __shared__ unsigned int call_s;
+    dg_pdl_launch_dependents();
+    DG_TL_IN(a.tl, DG_TL_P2P + a.chan);
+    dg_pdl_wait();
+    if (threadIdx.x == 0) call_s = ++(a.sig[a.rank] + a.chan)->calls[blockIdx.x];
+    __syncthreads();
+    const unsigned int call = call_s;
+    const size_t per = (a.n4 + a.world - 1) / a.world;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    const float4 *mine = reinterpret_cast<const float4 *>(a.buf[a.rank]);
+    for (int o = 0; o < a.world; ++o) {
+        if (o == a.rank) continue;
+        const size_t lo = per * o < a.n4 ? per * o : a.n4, hi = per * (o + 1) < a.n4 ? per * (o + 1) : a.n4;
+        float4 *dst = reinterpret_cast<float4 *>(a.stage[o]) + per * a.rank;
+        for (size_t i = lo + tid; i < hi; i += 2 * stride) {
+            const size_t i2 = i + stride;
+            const float4 v = p2p_ld_v4(mine + i);
+            float4 w = v;
+            if (i2 < hi) w = p2p_ld_v4(mine + i2);
+            p2p_st_v4(dst + (i - lo), v);
+            if (i2 < hi) p2p_st_v4(dst + (i2 - lo), w);
+        }
+    }
+    p2p_barrier(a, &P2PSignals::begin, call);
+    DG_TL_GO(a.tl, DG_TL_P2P + a.chan);
+    {
+        const size_t lo = per * a.rank < a.n4 ? per * a.rank : a.n4, hi = per * (a.rank + 1) < a.n4 ? per * (a.rank + 1) : a.n4;
+        const float4 *st = reinterpret_cast<const float4 *>(a.stage[a.rank]);
+        for (size_t i = lo + tid; i < hi; i += stride) {
+            float4 v[DG_MAX_RANKS];
+#pragma unroll
+            for (int r = 0; r < DG_MAX_RANKS; ++r)
+                if (r < a.world) v[r] = r == a.rank ? p2p_ld_v4(mine + i) : p2p_ld_v4(st + per * r + (i - lo));
+            float4 s = v[0];
+#pragma unroll
+            for (int r = 1; r < DG_MAX_RANKS; ++r)
+                if (r < a.world) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }      // rank order: the same bits every run
+#pragma unroll
+            for (int r = 0; r < DG_MAX_RANKS; ++r)
+                if (r < a.world) p2p_st_v4(reinterpret_cast<float4 *>(a.buf[r]) + i, s);
+        }
+    }
+    p2p_barrier(a, &P2PSignals::end, call);
+    DG_TL_OUT(a.tl, DG_TL_P2P + a.chan);
+}
+
 struct dg_p2p {
     P2PArgs args;
-    void *opened[2 * DG_MAX_RANKS];
+    void *opened[3 * DG_MAX_RANKS];
     int n_opened = 0;
     P2PSignals *sig_local = nullptr;
+    float *stage_local = nullptr;
 };
 
 // collective over the ranks of the context: map every rank's `buf` (a cudaMalloc base pointer of `nfloats` floats); 0 = ready.
@@ -199,9 +254,12 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
     dg_p2p *p = new dg_p2p();
     DG_CUDA(cudaMalloc((void **)&p->sig_local, 2 * sizeof(P2PSignals)));
     DG_CUDA(cudaMemset(p->sig_local, 0, 2 * sizeof(P2PSignals)));
-    struct Rec { cudaIpcMemHandle_t buf, sig; int dev; int ok; };
+    const size_t per4 = (nfloats / 4 + c->world - 1) / c->world;
+    DG_CUDA(cudaMalloc((void **)&p->stage_local, per4 * c->world * 16));
+    struct Rec { cudaIpcMemHandle_t buf, sig, stage; int dev; int ok; };
     Rec mine{}; mine.dev = c->dev; mine.ok = 1;
-    if (cudaIpcGetMemHandle(&mine.buf, buf) != cudaSuccess || cudaIpcGetMemHandle(&mine.sig, p->sig_local) != cudaSuccess) { cudaGetLastError(); mine.ok = 0; }
+    if (cudaIpcGetMemHandle(&mine.buf, buf) != cudaSuccess || cudaIpcGetMemHandle(&mine.sig, p->sig_local) != cudaSuccess ||
+        cudaIpcGetMemHandle(&mine.stage, p->stage_local) != cudaSuccess) { cudaGetLastError(); mine.ok = 0; }
     Rec *d_all = nullptr;
     DG_CUDA(cudaMalloc((void **)&d_all, sizeof(Rec) * (c->world + 1)));
     DG_CUDA(cudaMemcpy(d_all + c->world, &mine, sizeof(Rec), cudaMemcpyHostToDevice));
@@ -214,7 +272,7 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
     bool ok = true;
     for (int r = 0; r < c->world; ++r) ok = ok && all[r].ok;
     for (int r = 0; r < c->world && ok; ++r) {
-        if (r == c->rank) { p->args.buf[r] = buf; p->args.sig[r] = p->sig_local; continue; }
+        if (r == c->rank) { p->args.buf[r] = buf; p->args.sig[r] = p->sig_local; p->args.stage[r] = p->stage_local; continue; }
         int can = 0;
         if (cudaDeviceCanAccessPeer(&can, c->dev, all[r].dev) != cudaSuccess || !can) { ok = false; break; }
         cudaError_t pe = cudaDeviceEnablePeerAccess(all[r].dev, 0);
@@ -225,7 +283,10 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
         p->opened[p->n_opened++] = pb;
         if (cudaIpcOpenMemHandle(&ps, all[r].sig, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = false; break; }
         p->opened[p->n_opened++] = ps;
-        p->args.buf[r] = (float *)pb; p->args.sig[r] = (P2PSignals *)ps;
+        void *pg = nullptr;
+        if (cudaIpcOpenMemHandle(&pg, all[r].stage, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = false; break; }
+        p->opened[p->n_opened++] = pg;
+        p->args.buf[r] = (float *)pb; p->args.sig[r] = (P2PSignals *)ps; p->args.stage[r] = (float *)pg;
     }
     cudaGetLastError();
     // every rank must take the same path: agree on success through one more tiny allgather
@@ -253,6 +314,7 @@ void dg_dp_p2p_destroy(dg_p2p *p) {
     if (!p) return;
     for (int i = 0; i < p->n_opened; ++i) cudaIpcCloseMemHandle(p->opened[i]);
     cudaFree(p->sig_local);
+    cudaFree(p->stage_local);
     delete p;
 }
 
@@ -262,7 +324,9 @@ int dg_dp_p2p_allreduce(dg_ctx *c, dg_p2p *p, cudaStream_t st, size_t off, size_
     DG_REQUIRE(off % 4 == 0 && n % 4 == 0 && chan >= 0 && chan < 2, "peer exchange: bad range");
     P2PArgs a = p->args;
     a.off4 = off / 4; a.n4 = n / 4; a.chan = chan; a.tl = c->tl; a.scatter_only = scatter_only;
-    DG_CUDA(dg_launch_pdl(p2p_allreduce_kernel, dim3(DG_P2P_BLOCKS), dim3(512), 0, st, a));
+    static const bool push_rs = getenv("DG_DP_WRITE") != nullptr;      // the write-only variant, for comparison
+    if (!scatter_only && push_rs && off == 0 && n / 4 == p->args.n4) DG_CUDA(dg_launch_pdl(p2p_push_allreduce_kernel, dim3(DG_P2P_BLOCKS), dim3(512), 0, st, a));
+    else DG_CUDA(dg_launch_pdl(p2p_allreduce_kernel, dim3(DG_P2P_BLOCKS), dim3(512), 0, st, a));
     c->launches++;
     return 0;
 }
