@@ -275,6 +275,7 @@ extern "C" int dg_model_destroy(dg_model *m) {
     for (float *p : m->act) if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) if (m->dz[i]) cudaFree(m->dz[i]);
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
+    if (m->h_meta) { cudaFreeHost(m->h_meta); for (int i = 0; i < 4; ++i) cudaEventDestroy(m->ev_meta[i]); }
     cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
     cudaFree(m->d_loss); cudaFree(m->d_errors); cudaFree(m->d_rate); cudaFreeHost(m->h_rate);
     if (m->step_graph) cudaGraphExecDestroy(m->step_graph);
@@ -339,18 +340,32 @@ extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uin
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
     DG_CUDA(cudaMemcpyAsync(m->d_raw, raw, (size_t)n * DG_RAW_PLANES * DG_POINTS, cudaMemcpyHostToDevice, c->stream));
-    DG_CUDA(cudaMemcpyAsync(m->d_player, player, n, cudaMemcpyHostToDevice, c->stream));
-    DG_CUDA(cudaMemcpyAsync(m->d_rank, rank, n, cudaMemcpyHostToDevice, c->stream));
-    if (sym) DG_CUDA(cudaMemcpyAsync(m->d_sym, sym, n, cudaMemcpyHostToDevice, c->stream));
-    else DG_CUDA(cudaMemsetAsync(m->d_sym, 0, n, c->stream));
     m->n = n; m->have_raw = true; m->forward_done = false;
     m->have_targets = x != nullptr;
-    if (x) {
+    if (x)
         for (int i = 0; i < n; ++i)
             DG_REQUIRE(x[i] >= 1 && x[i] <= 19 && y[i] >= 1 && y[i] <= 19, "move %d: (%d,%d) outside the board", i, x[i], y[i]);
-        DG_CUDA(cudaMemcpyAsync(m->d_x, x, n, cudaMemcpyHostToDevice, c->stream));
-        DG_CUDA(cudaMemcpyAsync(m->d_y, y, n, cudaMemcpyHostToDevice, c->stream));
-        if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
+    {
+        // player / rank / sym / x / y are rows of one device block: gather them in a pinned staging slot and send ONE copy instead of
+        // five (each small copy costs a few microseconds of stream time).  Four slots, an event each: a slot is reused only after its
+        // copy has completed.
+        const size_t B = (size_t)m->max_batch;
+        if (!m->h_meta) {
+            DG_CUDA(cudaMallocHost((void **)&m->h_meta, 4 * 5 * B));
+            for (int i = 0; i < 4; ++i) DG_CUDA(cudaEventCreateWithFlags(&m->ev_meta[i], cudaEventDisableTiming));
+        }
+        const int slot = m->meta_slot++ & 3;
+        DG_CUDA(cudaEventSynchronize(m->ev_meta[slot]));
+        uint8_t *h = m->h_meta + (size_t)slot * 5 * B;
+        memcpy(h, player, n); memcpy(h + B, rank, n);
+        if (sym) memcpy(h + 2 * B, sym, n); else memset(h + 2 * B, 0, n);
+        if (x) { memcpy(h + 3 * B, x, n); memcpy(h + 4 * B, y, n); }
+        DG_CUDA(cudaMemcpyAsync(m->d_player, h, x ? 4 * B + n : 2 * B + n, cudaMemcpyHostToDevice, c->stream));
+        DG_CUDA(cudaEventRecord(m->ev_meta[slot], c->stream));
+    }
+    if (x) {
+        // the bf16 path's encode kernel computes the labels as well (one launch less per batch)
+        if (m->prec == DG_PREC_FP32 || dg_bf16_input_mode_fused()) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
     }
     if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]);
     return dg_bf16_stage_raw(m);
@@ -362,7 +377,7 @@ extern "C" int dg_model_encode_resident(dg_model *m) {
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
     m->forward_done = false;
-    if (m->have_targets) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, m->n, m->d_targets)) return rc;
+    if (m->have_targets && (m->prec == DG_PREC_FP32 || dg_bf16_input_mode_fused())) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, m->n, m->d_targets)) return rc;
     if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, m->n, m->act[0]);
     return dg_bf16_stage_raw(m);
 }
@@ -401,6 +416,7 @@ static int forward_impl(dg_model *m) {
         if (int rc = dg_bf16_forward(m)) return rc;
     }
     m->forward_done = true;
+    m->loss_reduced = false;           // a new forward pass: the reduction of the previous one is stale
     return 0;
 }
 
@@ -429,7 +445,7 @@ static int backward_impl(dg_model *m) {
 
 static int read_loss(dg_model *m, float *loss_out, int *errors_out) {
     dg_ctx *c = m->ctx;
-    if (int rc = dg_launch_loss_reduce(c, m->d_loss_n, m->d_argmax, m->d_targets, m->n, m->d_loss, m->d_errors)) return rc;
+    if (!m->loss_reduced) if (int rc = dg_launch_loss_reduce(c, m->d_loss_n, m->d_argmax, m->d_targets, m->n, m->d_loss, m->d_errors)) return rc;
     if (loss_out) DG_CUDA(cudaMemcpyAsync(loss_out, m->d_loss, 4, cudaMemcpyDeviceToHost, c->stream));
     if (errors_out) DG_CUDA(cudaMemcpyAsync(errors_out, m->d_errors, 4, cudaMemcpyDeviceToHost, c->stream));
     DG_CUDA(cudaStreamSynchronize(c->stream));
@@ -516,6 +532,7 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
         c->launches += m->step_graph_launches;
         dg_bf16_after_fused_step(m);
         m->forward_done = true;
+        m->loss_reduced = m->bf != nullptr;       // the captured backward pass reduces the loss
     } else {
         if (int rc = train_step_body(m, rate, false)) return rc;
     }

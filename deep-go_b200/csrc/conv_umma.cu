@@ -1384,10 +1384,33 @@ __global__ void __launch_bounds__(384, 1) head_umma_kernel(const HeadParams p) {
 
 // gW[i] += sum_n part[n][i] (i < 9C) ; ga[pt] += sum_n dz[n][pt] ; gb += sum_{n,pt} dz   -- fixed summation order.
 // A block owns 32 columns; its 8 warps take the positions n = w, w+8, .. and the partial sums meet in shared memory.
+// The block after the last column block reduces the step's loss (mean NLL, fixed order) and top-1 error count, so reading the loss
+// after dg_train_step needs no further kernel.
 __global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__restrict__ part, int n, int C, float *__restrict__ gW,
-                                                               float *__restrict__ gb, float *__restrict__ ga) {
+                                                               float *__restrict__ gb, float *__restrict__ ga,
+                                                               const float *__restrict__ loss_n, const int32_t *__restrict__ argmax,
+                                                               const int32_t *__restrict__ targets, float *__restrict__ loss_out,
+                                                               int *__restrict__ errors_out) {
     __shared__ float red[8][32];
     const int width = 9 * C + DG_POINTS;
+    if (blockIdx.x * 32 >= width) {
+        __shared__ float sl[256];
+        __shared__ int se[256];
+        float s = 0.f;
+        int e = 0;
+        for (int i = threadIdx.x; i < n; i += 256) {
+            s += loss_n[i];
+            if (argmax && targets) e += argmax[i] != targets[i];
+        }
+        sl[threadIdx.x] = s; se[threadIdx.x] = e;
+        __syncthreads();
+        for (int w = 128; w > 0; w >>= 1) {
+            if (threadIdx.x < w) { sl[threadIdx.x] += sl[threadIdx.x + w]; se[threadIdx.x] += se[threadIdx.x + w]; }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) { *loss_out = sl[0] / (float)n; *errors_out = se[0]; }
+        return;
+    }
     const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
     const int i = blockIdx.x * 32 + lane;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
@@ -1421,10 +1444,20 @@ __global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__re
 // definitions as encode.cu (dataloader.lua:50-92)
 __global__ void __launch_bounds__(384) encode_blocked_kernel(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ player,
                                                             const uint8_t *__restrict__ rank, const uint8_t *__restrict__ sym,
-                                                            bf16 *__restrict__ out, int R, int pitch, int pad) {
+                                                            bf16 *__restrict__ out, int R, int pitch, int pad,
+                                                            const uint8_t *__restrict__ mx, const uint8_t *__restrict__ my, int32_t *__restrict__ targets) {
     const int n = blockIdx.x, p = threadIdx.x;
     dg_pdl_launch_dependents();
     dg_pdl_wait();
+    if (p == DG_POINTS && targets) {
+        // the move label of the position (dataloader.lua:89), transformed like the board: saves the separate labels launch
+        int a = mx[n] - 1, b = my[n] - 1;
+        const int sy = sym ? sym[n] : 0;
+        if (sy & 1) { int t = a; a = b; b = t; }
+        if (sy & 2) a = DG_BOARD - 1 - a;
+        if (sy & 4) b = DG_BOARD - 1 - b;
+        targets[n] = DG_BOARD * a + b;
+    }
     if (p >= DG_POINTS) return;
     const int src = dg_src_point_d(p, sym ? sym[n] : 0);
     const uint8_t *rec = raw + (size_t)n * DG_RAW_PLANES * DG_POINTS;
@@ -2084,7 +2117,8 @@ int dg_bf16_stage_raw(dg_model *m) {
     if (fused && b->ops[0].cin_pad == 48) { b->x0_from_raw = true; return 0; }
     b->x0_from_raw = false;
     { dg_prof_scope _ps(c, DG_K_ENCODE);
-    DG_CUDA(dg_launch_pdl(encode_blocked_kernel, dim3(m->n), dim3(384), 0, c->stream, (const uint8_t *)m->d_raw, (const uint8_t *)m->d_player, (const uint8_t *)m->d_rank, (const uint8_t *)m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad));
+    DG_CUDA(dg_launch_pdl(encode_blocked_kernel, dim3(m->n), dim3(384), 0, c->stream, (const uint8_t *)m->d_raw, (const uint8_t *)m->d_player, (const uint8_t *)m->d_rank, (const uint8_t *)m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad,
+                          (const uint8_t *)m->d_x, (const uint8_t *)m->d_y, m->have_targets ? m->d_targets : (int32_t *)nullptr));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
@@ -2092,6 +2126,7 @@ int dg_bf16_stage_raw(dg_model *m) {
 }
 // 1: the next forward pass starts from raw records (fused encode), 0: from the blocked image in HBM -- two different step graphs
 int dg_bf16_input_mode(const dg_model *m) { return m->bf->x0_from_raw ? 1 : 0; }
+bool dg_bf16_input_mode_fused() { static const bool f = getenv("DG_FUSED_ENCODE") != nullptr; return f; }
 
 int dg_bf16_stage_planes(dg_model *m) {
     Bf16Path *b = m->bf;
@@ -2246,7 +2281,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
         const bool to_acc = m->fused_step && b->defer_grads;
         float *hW = to_acc ? b->gacc : m->grads + lh.offW, *hb = to_acc ? b->gacc + lh.nW : m->grads + lh.offB;
         float *ha = to_acc ? b->gacc + lh.nW + lh.cout : m->grads + lh.offA;
-        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32, 256, 0, hst>>>(b->head_part, m->n, m->C, hW, hb, ha);
+        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32 + 1, 256, 0, hst>>>(b->head_part, m->n, m->C, hW, hb, ha, m->d_loss_n, m->d_argmax,
+                                                                                           m->d_targets, m->d_loss, m->d_errors);
+        m->loss_reduced = true;
         c->launches++;
     }
     // bias gradients of every conv layer: side stream, all dZ are ready

@@ -19,6 +19,10 @@ struct dg_model {
     int32_t *d_targets = nullptr, *d_argmax = nullptr;
     float *d_logp = nullptr, *d_loss_n = nullptr, *d_loss = nullptr;
     int *d_errors = nullptr;
+    uint8_t *h_meta = nullptr;         // pinned staging ring for the small per-position arrays of dg_model_set_batch_raw
+    cudaEvent_t ev_meta[4] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned meta_slot = 0;
+    bool loss_reduced = false;         // d_loss / d_errors already hold the reduction of the last pass (done inside the backward pass)
     // captured CUDA graph of one fused training step (bf16 path, single GPU)
     cudaGraphExec_t step_graph = nullptr;
     int step_graph_n = 0;
@@ -39,6 +43,7 @@ int dg_bf16_params_changed(dg_model *m);
 int dg_bf16_sgd_step(dg_model *m, float rate, const float *rate_dev);   // fused SGD update + operand repack                 // refresh bf16 operand copies from the fp32 master
 int dg_bf16_stage_planes(dg_model *m);                   // act[0] (fp32 NCHW) -> blocked bf16 input image
 int dg_bf16_stage_raw(dg_model *m);                      // raw records -> blocked bf16 input image (deferred into the first conv kernel)
+bool dg_bf16_input_mode_fused();                         // DG_FUSED_ENCODE=1: no separate encode kernel (labels need their own launch then)
 int dg_bf16_input_mode(const dg_model *m);               // 1: the next forward pass encodes raw records itself
 int dg_bf16_forward(dg_model *m);                        // fills m->d_logp-ready logits via head
 int dg_bf16_backward(dg_model *m, float scale);
