@@ -1582,6 +1582,16 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
     constexpr int NB = (CO_B * DG_POINTS + NT - 1) / NT;      // per-point bias elements per thread
     const bool from_acc = L.gacc != nullptr;
     if (threadIdx.x < CO_B) bsum[threadIdx.x] = 0.f;
+    // the block is a chain of dependent global round trips: the master weights are requested first, together with the gradient
+    float *Wp = L.W + (size_t)co0 * row;
+    const int total = nco * row;
+    constexpr int NPRE = 20;                        // covers CO_B * 9 * 128 / NT = 18 elements per thread
+    float wpre[NPRE];
+#pragma unroll
+    for (int k = 0; k < NPRE; ++k) {
+        const int i = threadIdx.x + k * NT;
+        wpre[k] = i < total ? Wp[i] : 0.f;
+    }
     if (from_acc) {
         // the accumulation buffer [tap][cin/4][cout][4] is read in ITS order (8 output channels x 16 bytes = one 128-byte line) and
         // transposed through shared memory into the rows the sweep below walks
@@ -1602,9 +1612,7 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
     // ---- weights: update in place, keep the new values in shared memory.  The 8 rows are contiguous in the master vector: a flat,
     // coalesced sweep; the block is latency-bound, so every thread first issues all its loads (weights, gradients, and the
     // per-point bias of the next phase) and only then computes
-    float *Wp = L.W + (size_t)co0 * row;
     const float *Gp = L.gW + (size_t)co0 * row;
-    const int total = nco * row;
     float av[NB], ag[NB];                           // per-point bias: nco * 361 elements
 #pragma unroll
     for (int k = 0; k < NB; ++k) {
@@ -1634,27 +1642,23 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
             if ((threadIdx.x & 31) == 0) { bpart[k][threadIdx.x >> 5][0] = s_lo; bpart[k][threadIdx.x >> 5][1] = s_hi; }
         }
     }
-    for (int base = threadIdx.x; base < total; base += 12 * NT) {
-        float wv[12], gv[12];
 #pragma unroll
-        for (int k = 0; k < 12; ++k) {
-            const int i = base + k * NT;
-            wv[k] = gv[k] = 0.f;
-            if (i < total) {
-                wv[k] = Wp[i];
-                if (from_acc) { const int r = i / row; gv[k] = wrow[r * smem_row + (i - r * row)]; }
-                else gv[k] = __ldcg(sgd_grad_ptr(peers, Gp + i));
-            }
+    for (int k = 0; k < NPRE; ++k) {
+        const int i = threadIdx.x + k * NT;
+        if (i < total) {
+            const int r = i / row;
+            const float g = from_acc ? wrow[r * smem_row + (i - r * row)] : __ldcg(sgd_grad_ptr(peers, Gp + i));
+            const float v = fmaf(neg_rate, g, wpre[k]);
+            Wp[i] = v;
+            if (L.wf) wrow[r * smem_row + (i - r * row)] = v;
         }
-#pragma unroll
-        for (int k = 0; k < 12; ++k) {
-            const int i = base + k * NT;
-            if (i < total) {
-                const float v = fmaf(neg_rate, gv[k], wv[k]);
-                Wp[i] = v;
-                if (L.wf) { const int r = i / row; wrow[r * smem_row + (i - r * row)] = v; }
-            }
-        }
+    }
+    for (int i = threadIdx.x + NPRE * NT; i < total; i += NT) {      // wider layers: the rest, one element at a time
+        const int r = i / row;
+        const float g = from_acc ? wrow[r * smem_row + (i - r * row)] : __ldcg(sgd_grad_ptr(peers, Gp + i));
+        const float v = fmaf(neg_rate, g, Wp[i]);
+        Wp[i] = v;
+        if (L.wf) wrow[r * smem_row + (i - r * row)] = v;
     }
     if (from_acc) {
         __syncthreads();
