@@ -714,6 +714,65 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
             float4 *gl = reinterpret_cast<float4 *>(p.gacc[li]);
             // scratch tile layout [kx][ci/4][co][4]: lane = co, so one warp-wide 16-byte access covers 512 contiguous bytes
             float4 *sc = reinterpret_cast<float4 *>(p.scratch) + ((size_t)combo * p.splits + split) * p.ksize * 32 * p.nb + (q * 32 + lane);
+            if (gl && p.ksize == 3 && p.nb == 128) {
+                // Fast path (3x3 layers): the reductions are bound by L2 atomic throughput (all CTAs drain at once), and an MMA warp can
+                // only start the next layer when its accumulator has been READ.  So: read two kernel columns into registers and hand
+                // them back at once, then issue the reductions -- warps 0 and 1 restart ~100 cycles after they finish, warp 2 after a
+                // third of the drain instead of all of it.
+                uint32_t ra[2][32], rb2[2][32];
+                const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16);
+                auto ld_kx = [&](int kx, uint32_t (&r)[2][32]) {
+                    tmem_ld32(tq + kx * 128 + half * 32, r[0]);
+                    tmem_ld32(tq + kx * 128 + half * 32 + 64, r[1]);
+                    tmem_ld_wait();
+                };
+                auto red_kx = [&](int kx, const uint32_t (&r)[2][32]) {
+                    if (!(any && co < p.cout)) return;
+#pragma unroll
+                    for (int bk = 0; bk < 2; ++bk) {
+                        float4 *o = gl + ((size_t)(ky * 3 + kx) * cin4 + nblk * 32 + ((half * 32 + bk * 64) >> 2)) * p.cout + co;
+#pragma unroll
+                        for (int g = 0; g < 8; ++g)
+                            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + (size_t)g * p.cout), "f"(__uint_as_float(r[bk][g * 4])),
+                                         "f"(__uint_as_float(r[bk][g * 4 + 1])), "f"(__uint_as_float(r[bk][g * 4 + 2])), "f"(__uint_as_float(r[bk][g * 4 + 3]))
+                                         : "memory");
+                    }
+                };
+                auto release = [&](int w) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(&acc_empty[w]); };
+                mbar_wait(&acc_full[0], lc & 1);
+                tc_fence_after();
+                ld_kx(0, ra);
+                if (fused_bias) {
+                    const int panel = split % panels;
+                    float4 *gb4 = reinterpret_cast<float4 *>(p.gab[li]);
+                    for (int ks = ky + half * 3; ks < WG_RP / 16; ks += 6) {
+                        uint32_t r[32];
+                        tmem_ld16(tq + bias_col + 16u * ks, r);
+                        tmem_ld_wait();
+                        if (any && co < p.cout) {
+                            float4 *o = gb4 + (size_t)((panel * WG_RP + 16 * ks) >> 2) * p.cout + co;
+#pragma unroll
+                            for (int g = 0; g < 4; ++g)
+                                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + (size_t)g * p.cout), "f"(__uint_as_float(r[g * 4])),
+                                             "f"(__uint_as_float(r[g * 4 + 1])), "f"(__uint_as_float(r[g * 4 + 2])), "f"(__uint_as_float(r[g * 4 + 3]))
+                                             : "memory");
+                        }
+                    }
+                }
+                release(0);
+                mbar_wait(&acc_full[1], lc & 1);
+                tc_fence_after();
+                ld_kx(1, rb2);
+                release(1);
+                red_kx(0, ra);
+                mbar_wait(&acc_full[2], lc & 1);
+                tc_fence_after();
+                ld_kx(2, ra);
+                release(2);
+                red_kx(1, rb2);
+                red_kx(2, ra);
+                continue;
+            }
             for (int w = 0; w < CONV_MMA_WARPS; ++w) {
             mbar_wait(&acc_full[w], lc & 1);
             tc_fence_after();
