@@ -147,3 +147,28 @@ def test_full_size_properties(golden):
     assert np.linalg.norm(g_full) > 0
     l0 = m.train_step(0.02); l1 = m.train_step(0.02); l2 = m.train_step(0.02)
     assert l2 < l0
+
+
+def test_gradient_vector_after_fused_step(golden):
+    """dg_train_step leaves the conv gradients in the accumulation buffers (the SGD kernel reads them there); the Torch7-order
+    vector is built on demand.  With rate 0 the parameters do not move, so the vector read after a fused step must equal the one
+    of the separate calls zero_grads / forward / loss_backward on the same batch -- twice in a row (graph replay) and after
+    switching between the two call styles."""
+    from oracle import net
+    L, C, n = 5, 128, 16
+    flat = net.init_params(L, C, 21, "he")
+    m = _model(L, C, n, flat)
+    b = U.sample(golden, n, 31)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    m.forward(False); m.zero_grads(); loss_sep = m.loss_backward()
+    g_sep = m.get_grads()
+    assert np.linalg.norm(g_sep) > 0
+    for _ in range(2):
+        m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+        loss_fused = m.train_step(0.0)
+        g_fused = m.get_grads()
+        assert abs(loss_fused - loss_sep) < 1e-5
+        assert U.rel(g_fused, g_sep) < 1e-4                      # same kernels, only the summation order of the L2 reductions differs
+    assert np.array_equal(m.get_params(), flat.numpy().astype(np.float32))
+    m.forward(False); m.zero_grads(); m.loss_backward()
+    assert U.rel(m.get_grads(), g_sep) < 1e-4
