@@ -129,7 +129,7 @@ __device__ __forceinline__ void p2p_barrier(const P2PArgs &a, unsigned int (P2PS
         const unsigned int *mine = &((a.sig[a.rank] + a.chan)->*which)[blockIdx.x][threadIdx.x];
         unsigned long long spins = 0;
         while (p2p_ld_acquire_sys(mine) != call)
-            if (++spins > (1ull << 31)) __trap();
+            if (++spins > (1ull << 27)) __trap();      // ~2 minutes of polling: a peer that never arrives kills the step instead of hanging the GPU
     }
     __syncthreads();
 }
