@@ -70,3 +70,65 @@ def do_queued_tasks():
     while _queued:
         job, filenames, f = _queued.pop(0)
         f(job.result() if job is not None else dataloader.load_minibatch(filenames))
+
+
+# ---- packed corpus: the same positions, one file, native loader --------------------------------------
+class Corpus:
+    """One packed file instead of one Torch7 file per position (dg_corpus_* in include/deepgo.h).  `raw_minibatch(n)` returns what
+    Model.set_batch_raw takes; positions are drawn uniformly (the reference draws a uniform game, then a uniform move of it,
+    data.lua:29-37 -- pass `indices` to reproduce any other sampling)."""
+
+    def __init__(self, path, threads=8):
+        from deepgo_b200 import ffi, lib, check
+        self._ffi, self._lib, self._check = ffi, lib(), check
+        h = ffi.new("dg_corpus **")
+        check(self._lib.dg_corpus_open(str(path).encode(), h))
+        self.h = ffi.gc(h[0], self._lib.dg_corpus_close)
+        n = ffi.new("long long *")
+        check(self._lib.dg_corpus_count(self.h, n))
+        self.count = int(n[0])
+        self.threads = threads
+
+    @staticmethod
+    def pack(filenames, out_path, threads=8):
+        """Pack Torch7 record files (dataloader.lua:123-125 reads them one by one) into one corpus file."""
+        from deepgo_b200 import ffi, lib, check
+        keep = [ffi.new("char[]", str(f).encode()) for f in filenames]
+        arr = ffi.new("const char *[]", keep)
+        check(lib().dg_corpus_pack(arr, len(keep), str(out_path).encode(), threads))
+        return out_path
+
+    def read(self, indices, want_moves=True):
+        import numpy as np
+        idx = np.ascontiguousarray(indices, dtype=np.int64)
+        n = len(idx)
+        raw = np.empty((n, 9, 19, 19), np.uint8)
+        pl, rk = np.empty(n, np.uint8), np.empty(n, np.uint8)
+        x, y = (np.empty(n, np.uint8), np.empty(n, np.uint8)) if want_moves else (None, None)
+        c = lambda a: self._ffi.cast("uint8_t *", a.ctypes.data) if a is not None else self._ffi.NULL
+        self._check(self._lib.dg_corpus_read_batch(self.h, self._ffi.cast("const long long *", idx.ctypes.data), n, c(raw), c(pl), c(rk),
+                                                   c(x), c(y), self.threads))
+        return {"raw": raw, "player": pl, "rank": rk, "x": x, "y": y}
+
+    def raw_minibatch(self, n, rng=None):
+        import numpy as np
+        rng = rng or np.random.default_rng()
+        return self.read(rng.integers(0, self.count, n))
+
+
+def write_corpus_from_arrays(path, raw, x, y, player, ranks):
+    """The packed format written from arrays (fixtures, synthetic corpora): 64-byte header + 3,264-byte records
+    (deep-go_b200/csrc/corpus.cpp)."""
+    import numpy as np
+    n = len(raw)
+    rec = np.zeros((n, 3264), np.uint8)
+    rec[:, :3249] = np.asarray(raw, np.uint8).reshape(n, 3249)
+    rec[:, 3249] = x; rec[:, 3250] = y; rec[:, 3251] = player
+    rec[:, 3252:3254] = np.asarray(ranks, np.uint8).reshape(n, 2)
+    hdr = np.zeros(64, np.uint8)
+    hdr[:8] = np.frombuffer(b"DGCORP01", np.uint8)
+    hdr[8:16] = np.frombuffer(np.uint64(n).tobytes(), np.uint8)
+    hdr[16:20] = np.frombuffer(np.uint32(3264).tobytes(), np.uint8)
+    with open(path, "wb") as f:
+        f.write(hdr.tobytes()); f.write(rec.tobytes())
+    return path

@@ -108,6 +108,21 @@ int dg_encode_labels(const uint8_t *x, const uint8_t *y, const uint8_t *sym, int
  * 1-based move / player / ranks exactly as stored.  Host-only, reentrant (loader threads, data.lua:14-19). */
 int dg_t7_read_record(const char *path, uint8_t *raw, int *x, int *y, int *player, int ranks[2]);
 
+/* ---- packed corpus + native minibatch loader -------------------------------- */
+/* The reference keeps one Torch7 file per position and loads a minibatch with n torch.load calls in a pool of Lua threads
+ * (dataloader.lua:113-125, data.lua:14-19,29-37,82-92).  dg_corpus_pack reads n such files (nthreads host threads) and
+ * writes ONE file of fixed 3,264-byte records; dg_corpus_read_batch then assembles a minibatch -- the arguments of
+ * dg_model_set_batch_raw -- with n memcpys out of a read-only mapping.  Host only, reentrant per handle. */
+typedef struct dg_corpus dg_corpus;
+int dg_corpus_pack(const char *const *paths, long long n, const char *out_path, int nthreads);
+int dg_corpus_open(const char *path, dg_corpus **out);
+int dg_corpus_close(dg_corpus *c);
+int dg_corpus_count(dg_corpus *c, long long *out);
+/* records idx[0..n) -> raw u8[n][9][19][19], player u8[n], rank u8[n] (= ranks[player], dataloader.lua:87), and the
+ * 1-based move x, y u8[n] (both NULL: not wanted) */
+int dg_corpus_read_batch(dg_corpus *c, const long long *idx, int n, uint8_t *raw, uint8_t *player, uint8_t *rank,
+                         uint8_t *x, uint8_t *y, int nthreads);
+
 /* ---- board analysis (makedata.lua) --------------------------------------------------------- */
 /* summarize_board (makedata.lua:143-153): stones u8[n][19][19] in {0,1,2} ->
  * out u8[n][7][19][19]: liberties, liberties_after[p=1,2], kills[p=1,2], ladders[p=1,2]. */
