@@ -123,6 +123,15 @@ int dg_corpus_count(dg_corpus *c, long long *out);
 int dg_corpus_read_batch(dg_corpus *c, const long long *idx, int n, uint8_t *raw, uint8_t *player, uint8_t *rank,
                          uint8_t *x, uint8_t *y, int nthreads);
 
+/* ---- SGF front end (makedata.lua:24-120) ------------------------------------- */
+/* One game's SGF text -> dan ranks (get_ranks; *has_ranks = 0: the reference writes no record for such a game), handicap
+ * stones (handicaps) and the move list without passes (all_moves), coordinates 1-based, player 1 = black.  Follows the
+ * reference's tokenisation to the letter (lines end at CR LF only, a piece is a token only with exactly one '[' ...: see
+ * csrc/sgf.cpp).  The output arrays may be NULL to count only.  Host only, reentrant.  Feed the result to dg_update_boards /
+ * dg_summarize_boards (all_boards, makedata.lua:156-186: summarise BEFORE each move, then play it). */
+int dg_sgf_parse(const char *sgf, size_t len, int ranks[2], int *has_ranks, uint8_t *hx, uint8_t *hy, uint8_t *hplayer,
+                 int max_handicaps, int *n_handicaps, uint8_t *mx, uint8_t *my, uint8_t *mplayer, int max_moves, int *n_moves);
+
 /* ---- board analysis (makedata.lua) --------------------------------------------------------- */
 /* summarize_board (makedata.lua:143-153): stones u8[n][19][19] in {0,1,2} ->
  * out u8[n][7][19][19]: liberties, liberties_after[p=1,2], kills[p=1,2], ladders[p=1,2]. */
