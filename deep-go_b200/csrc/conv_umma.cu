@@ -295,8 +295,8 @@ __global__ void __launch_bounds__(384, 1) conv_umma_kernel(const __grid_constant
             }
             for (int l = 0; l < p.nchain; ++l)
                 for (int nbk = 0; nbk < nnb; ++nbk, ++a) {
-                    // the epilogue warps have drained the previous accumulators, written the previous layer's output rows
-                    // into the shared-memory image (chains) and, in forward mode, pre-loaded the accumulators with the bias
+                    // the epilogue warps have drained the previous accumulators and written the previous layer's output rows into
+                    // the shared-memory image (chains); the first MMA of every tile overwrites its accumulator
                     if (PAIR) mbar_wait_cluster(&acc_ready, a & 1);
                     else if (rotate && mma_id == 0) mbar_wait(&acc_ready01, a & 1);      // tile 0 may start before tile 2 of the previous layer is drained
                     else mbar_wait(&acc_ready, a & 1);

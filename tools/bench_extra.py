@@ -107,4 +107,18 @@ t0 = time.perf_counter(); ref = oboard.summarize(stones); dt_cpu = time.perf_cou
 out["board_analysis"] = {"boards": len(stones), "gpu_boards_per_s": len(stones) / dt_gpu, "cpu_oracle_boards_per_s": len(stones) / dt_cpu,
                          "cpu_threads": os.cpu_count(), "bit_exact": bool(np.array_equal(got, ref)),
                          "note": "dg_summarize_boards host to host (wall clock) vs the C oracle with OpenMP over boards"}
+# ---- SGF -> records (N4): the 22 fixture games re-transcribed from synthesised SGF text, host to host ---------------------
+from deepgo_b200.host import makedata
+LET = "abcdefghijklmnopqrs"
+texts = []
+for gi in range(len(g["games"])):
+    sel = np.where(g["game"] == gi)[0]
+    sel = sel[np.argsort(g["move"][sel])]
+    texts.append("(;BR[%dd];WR[%dd]" % tuple(g["ranks"][sel[0]]) + "".join(
+        ";%s[%s%s]" % ("BW"[g["player"][i] - 1], LET[g["x"][i] - 1], LET[g["y"][i] - 1]) for i in sel) + ";)")
+texts = texts * 8                                                            # 176 games in lockstep
+makedata.transcribe(texts[:2], ctx)
+t0 = time.perf_counter(); rec = makedata.transcribe(texts, ctx); dt = time.perf_counter() - t0
+out["sgf_transcribe"] = {"games": len(texts), "records": int(len(rec["raw"])), "records_per_s": len(rec["raw"]) / dt,
+                         "note": "dg_sgf_parse + lockstep dg_update_boards (one call per move number) + one dg_summarize_boards; Python driver, wall clock"}
 print(json.dumps(out, indent=1))
