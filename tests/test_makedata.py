@@ -88,3 +88,29 @@ def test_handicap_replay_and_corpus(md, tmp_path):
     c = data.Corpus(tmp_path / "g.dgc")
     b = c.read([0, 1])
     assert np.array_equal(b["raw"], rec["raw"]) and list(b["rank"]) == [7, 5] and list(b["player"]) == [2, 1]
+
+
+def test_parser_against_the_python_restatement(md):
+    """dg_sgf_parse (C++) against oracle/sgf.py on random SGF-like text built from the characters that matter."""
+    import deepgo_b200
+    from hypothesis import given, settings, strategies as st
+    from oracle import sgf as osgf
+
+    atoms = st.sampled_from([";", "[", "]", "\r\n", "\n", "B", "W", "A", "R", "d", "k", "a", "s", "t", "p", "3", " ", ")", "(", "BR[", "WR[", "AB[", "]["])
+
+    @settings(max_examples=400, deadline=None)
+    @given(st.lists(atoms, max_size=40).map("".join))
+    def check(text):
+        ranks, moves, hc = osgf.get_ranks(text), osgf.all_moves(text), osgf.handicaps(text)
+        bad = any(m[1] is None for m in moves) or any(h[0] is None or h[1] is None for h in hc)
+        bad = bad or (ranks is not None and any(r != int(r) or not 0 <= r <= 255 for r in ranks))
+        try:
+            p = md.parse(text)
+        except deepgo_b200.DeepGoError:
+            assert bad, text
+            return
+        assert not bad, text
+        assert p["moves"] == moves and p["handicaps"] == hc
+        assert p["ranks"] == (None if ranks is None else (int(ranks[0]), int(ranks[1])))
+
+    check()
