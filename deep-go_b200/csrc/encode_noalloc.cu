@@ -5,8 +5,7 @@
 //   * loader threads that encode small batches while a training step is in flight on the same GPU -- cudaMalloc
 //     and cudaFree synchronise the whole device, so one allocation in a loader stalls the step it runs beside;
 //   * processes where another framework's caching allocator has already reserved (nearly) all of HBM, so a
-//     cudaMalloc from this library simply fails;
-//   * code that runs between cudaStreamBeginCapture and EndCapture, where allocation calls are not allowed.
+//     cudaMalloc from this library simply fails.
 // For them the staging memory lives in the library image itself: a fixed, file-scope __device__ array.  Every GPU
 // that loads the library carries these DG_NOALLOC_SCRATCH_BYTES (about 3.7 MB) until the process exits, which is
 // why the limit is a modest 64 positions per call.

@@ -1,6 +1,7 @@
 """Host mirror of data.lua: Dataset index (:53-80), random (game, move) sampling (:29-37) and the
-queue_on_minibatch / do_queued_tasks pair (:82-96).  Jobs run on a thread pool (the record reader of the C
-library is reentrant); callbacks run on the caller's thread inside do_queued_tasks, as `threads` does."""
+queue_on_minibatch / do_queued_tasks pair (:82-96).  The pool threads only READ the record files (the record reader of the C
+library is reentrant); the batch is encoded on the device and the callback runs on the caller's thread inside
+do_queued_tasks, as `threads` does -- the loader's device context is never entered by two threads at once."""
 import os
 import random
 from concurrent.futures import ThreadPoolExecutor
@@ -62,14 +63,15 @@ def queue_on_minibatch(f, dataset, n, base=None):
         dataset.init()
     root = base if base is not None else getattr(dataset, "base", "")
     filenames = [os.path.join(root, dataset.generate_random_filename()) for _ in range(n)]
-    job = _pool.submit(dataloader.load_minibatch, filenames) if _pool else None
+    job = _pool.submit(dataloader.read_records, filenames) if _pool else None
     _queued.append((job, filenames, f))
 
 
 def do_queued_tasks():
     while _queued:
         job, filenames, f = _queued.pop(0)
-        f(job.result() if job is not None else dataloader.load_minibatch(filenames))
+        recs = job.result() if job is not None else dataloader.read_records(filenames)
+        f(dataloader.encode_records(recs))
 
 
 # ---- packed corpus: the same positions, one file, native loader --------------------------------------

@@ -10,6 +10,8 @@
   load_and_preprocess(filename) (:123-125)    load_and_preprocess(filename)
 `output` keeps the reference's 1-based class index; the C ABI takes 0-based targets (train.py subtracts 1).
 """
+import threading
+
 import numpy as np
 
 import deepgo_b200 as _dg
@@ -41,14 +43,24 @@ class _Input:
 
 INPUT = _Input()
 _ctx = None
+_ctx_lock = threading.Lock()
 
 
 def context(device=0):
-    """The device context the loader encodes on (created on first use)."""
+    """The device context the loader encodes on (created on first use).  A dg_ctx takes ONE caller thread at a time
+    (include/deepgo.h): encode calls go through encode_lock()."""
     global _ctx
-    if _ctx is None:
-        _ctx = engine.Context(device)
+    with _ctx_lock:
+        if _ctx is None:
+            _ctx = engine.Context(device)
     return _ctx
+
+
+_encode_lock = threading.Lock()
+
+
+def encode_lock():
+    return _encode_lock
 
 
 def flatten_data(data):
@@ -94,7 +106,8 @@ def _rank_of(data):
 def preprocess(data, sym=0):
     """One record -> 37 planes + label (dataloader.lua:50-92), encoded on the GPU."""
     mv = data["move"]
-    planes = context().encode(data["input"][None], [mv["player"]], [_rank_of(data)], [sym])[0]
+    with _encode_lock:
+        planes = context().encode(data["input"][None], [mv["player"]], [_rank_of(data)], [sym])[0]
     label0 = engine.encode_labels([mv["x"]], [mv["y"]], [sym])[0]
     return {"input": planes, "output": int(label0) + 1}
 
@@ -103,10 +116,15 @@ def empty_minibatch_io(size):
     return np.zeros([size] + input_dimensions, np.float32), np.zeros([size] + output_dimensions, np.float64)
 
 
-def load_minibatch(filenames, sym=None):
-    """dataloader.lua:113-121: read + encode a list of record files -> {"input": [n,37,19,19], "output": [n] (1-based)}.
-    The batch is encoded in ONE device call."""
-    recs = [read_record(f) for f in filenames]
+def read_records(filenames):
+    """The host-only half of load_minibatch: torch.load of every record (dg_t7_read_record is reentrant, so this is what
+    the loader threads of data.lua:14-19 run)."""
+    return [read_record(f) for f in filenames]
+
+
+def encode_records(recs, sym=None):
+    """The device half of load_minibatch: ONE encode call for the batch.  The loader's dg_ctx has a single stream and a
+    single staging buffer, so concurrent callers are serialised here."""
     inputs, outputs = empty_minibatch_io(len(recs))
     if recs:
         raw = np.stack([r["input"] for r in recs])
@@ -114,9 +132,15 @@ def load_minibatch(filenames, sym=None):
         rk = np.array([_rank_of(r) for r in recs], np.uint8)
         xs = np.array([r["move"]["x"] for r in recs], np.uint8)
         ys = np.array([r["move"]["y"] for r in recs], np.uint8)
-        inputs = context().encode(raw, pl, rk, sym)
+        with _encode_lock:
+            inputs = context().encode(raw, pl, rk, sym)
         outputs = engine.encode_labels(xs, ys, sym).astype(np.float64) + 1
     return {"input": inputs, "output": outputs, "records": recs}
+
+
+def load_minibatch(filenames, sym=None):
+    """dataloader.lua:113-121: read + encode a list of record files -> {"input": [n,37,19,19], "output": [n] (1-based)}."""
+    return encode_records(read_records(filenames), sym)
 
 
 def load_and_preprocess(filename):

@@ -92,9 +92,9 @@ int dg_encode(dg_ctx *ctx, const uint8_t *raw, const uint8_t *player, const uint
               const uint8_t *sym, int n, void *out, int outfmt);
 /* dg_encode for callers that cannot allocate device memory.  No counterpart in the reference: this entry point exists
  * only because of how the library is embedded.  Loader threads that must not stall a running training step
- * (cudaMalloc/cudaFree synchronise the device), processes whose HBM is already owned by another allocator, and code
- * between stream-capture begin/end cannot let dg_encode grow its staging buffer; this variant stages through a fixed
- * ~3.7 MB array that is part of the library image on every GPU.  Same arguments and results as dg_encode, but
+ * (cudaMalloc/cudaFree synchronise the device) and processes whose HBM is already owned by another allocator
+ * cannot let dg_encode grow its staging buffer; this variant stages through a fixed ~3.7 MB array that is part of
+ * the library image on every GPU.  Like dg_encode it synchronises the context's stream before it returns.  Same arguments and results as dg_encode, but
  * n <= 64 (larger n is an error).  The first call on a device resolves the array's device address -- make it before
  * any stream capture.  Calls on one GPU share the array: run them one at a time (overlapping calls race); the array
  * keeps the last call's bytes and needs no clearing.  Calls no cudaMalloc/cudaFree. */
