@@ -245,8 +245,8 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     DG_CUDA(cudaMemsetAsync(m->params, 0, m->P * 4, c->stream));
     DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));
     DG_CUDA(cudaMalloc(&m->d_raw, B * DG_RAW_PLANES * DG_POINTS));
-    DG_CUDA(cudaMalloc(&m->d_player, B * 5));
-    m->d_rank = m->d_player + B; m->d_sym = m->d_rank + B; m->d_x = m->d_sym + B; m->d_y = m->d_x + B;
+    DG_CUDA(cudaMalloc(&m->d_player, B * 6));
+    m->d_rank = m->d_player + B; m->d_sym = m->d_rank + B; m->d_x = m->d_sym + B; m->d_y = m->d_x + B; m->d_sym_keep = m->d_y + B;
     DG_CUDA(cudaMalloc(&m->d_targets, B * 4));
     DG_CUDA(cudaMalloc(&m->d_argmax, B * 4));
     DG_CUDA(cudaMalloc(&m->d_logp, B * DG_POINTS * 4));
@@ -254,7 +254,8 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     DG_CUDA(cudaMalloc(&m->d_loss, 4));
     DG_CUDA(cudaMalloc(&m->d_errors, 4));
     DG_CUDA(cudaMalloc(&m->d_rate, 4));
-    DG_CUDA(cudaMallocHost(&m->h_rate, 4));
+    DG_CUDA(cudaMallocHost(&m->h_rate, 8 * 4));
+    for (int i = 0; i < 8; ++i) DG_CUDA(cudaEventCreateWithFlags(&m->ev_rate[i], cudaEventDisableTiming));
     m->act.assign(num_layers + 1, nullptr);
     DG_CUDA(cudaMalloc(&m->act[0], B * in_planes * DG_POINTS * 4));
     if (precision == DG_PREC_FP32) {
@@ -279,6 +280,7 @@ extern "C" int dg_model_destroy(dg_model *m) {
     cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
     cudaFree(m->d_loss); cudaFree(m->d_errors); cudaFree(m->d_rate); cudaFreeHost(m->h_rate);
     if (m->step_graph) cudaGraphExecDestroy(m->step_graph);
+    for (int i = 0; i < 8; ++i) if (m->ev_rate[i]) cudaEventDestroy(m->ev_rate[i]);
     dg_ctx *c = m->ctx;
     delete m;
     if (--c->live_models == 0 && c->zombie) { c->zombie = false; return dg_ctx_destroy(c); }
@@ -326,6 +328,12 @@ extern "C" int dg_zero_grads(dg_model *m) {
 }
 extern "C" int dg_model_set_global_batch(dg_model *m, int gb) {
     DG_REQUIRE(m && gb >= 0, "dg_model_set_global_batch: bad argument");
+    if (gb != m->global_batch && m->step_graph) {
+        // the captured step holds 1/global_batch as a by-value kernel argument: capture again
+        DG_CUDA(cudaSetDevice(m->ctx->dev));
+        DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
+        cudaGraphExecDestroy(m->step_graph); m->step_graph = nullptr;
+    }
     m->global_batch = gb;
     return 0;
 }
@@ -507,8 +515,11 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     const bool use_graph = m->prec == DG_PREC_BF16 && (c->world == 1 || !no_dp_graph) && !c->prof_on && !no_graph;
     if (use_graph) {
         // the ~50 launches and the cross-stream event edges of a step are captured once per batch size and replayed
-        *m->h_rate = rate;
-        DG_CUDA(cudaMemcpyAsync(m->d_rate, m->h_rate, 4, cudaMemcpyHostToDevice, c->stream));
+        const int rs = m->rate_slot++ & 7;
+        DG_CUDA(cudaEventSynchronize(m->ev_rate[rs]));      // the copy that last read this slot is done (8 steps ago)
+        m->h_rate[rs] = rate;
+        DG_CUDA(cudaMemcpyAsync(m->d_rate, m->h_rate + rs, 4, cudaMemcpyHostToDevice, c->stream));
+        DG_CUDA(cudaEventRecord(m->ev_rate[rs], c->stream));
         const int in_mode = dg_bf16_input_mode(m);
         if (!m->step_graph || m->step_graph_n != m->n || m->step_graph_mode != in_mode) {
             if (m->step_graph) { cudaGraphExecDestroy(m->step_graph); m->step_graph = nullptr; }

@@ -28,7 +28,12 @@ struct dg_model {
     int step_graph_n = 0;
     int step_graph_mode = 0;           // input mode the graph was captured in (raw records vs blocked image)
     long long step_graph_launches = 0;
-    float *d_rate = nullptr, *h_rate = nullptr;     // rate for the graph's SGD node (device scalar, pinned staging)
+    // rate for the graph's SGD node: device scalar, fed from a ring of pinned slots (a slot is rewritten only after the copy that
+    // reads it has completed: steps that return without a host sync would otherwise see the next step's rate)
+    float *d_rate = nullptr, *h_rate = nullptr;
+    cudaEvent_t ev_rate[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned rate_slot = 0;
+    uint8_t *d_sym_keep = nullptr;     // dg_predict_sym8: the caller's symmetry ids while the eight passes overwrite d_sym
     // fp32 path (NCHW)
     std::vector<float *> act;          // act[0] = input planes, act[l] = h_l
     float *dz[2] = {nullptr, nullptr};

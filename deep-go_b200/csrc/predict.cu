@@ -50,16 +50,19 @@ extern "C" int dg_predict_sym8(dg_model *m, float *probs_out, int32_t *argmax_ou
     if (int rc = dg_ctx_scratch(c, (size_t)m->n * DG_POINTS * 4, (void **)&acc)) return rc;
     const bool had_targets = m->have_targets;
     m->have_targets = false;                                   // pure inference: no NLL / target lookups
+    // the eight passes overwrite the staged symmetry ids: keep the caller's and put them back afterwards
+    DG_CUDA(cudaMemcpyAsync(m->d_sym_keep, m->d_sym, m->n, cudaMemcpyDeviceToDevice, c->stream));
+    auto restore = [&]() { m->have_targets = had_targets; cudaMemcpyAsync(m->d_sym, m->d_sym_keep, m->n, cudaMemcpyDeviceToDevice, c->stream); };
     for (int s = 0; s < 8; ++s) {
         fill_u8_kernel<<<(m->n + 255) / 256, 256, 0, c->stream>>>(m->d_sym, m->n, (uint8_t)s);
         c->launches++;
-        if (int rc = dg_model_encode_resident(m)) { m->have_targets = had_targets; return rc; }
-        if (int rc = dg_forward(m, nullptr)) { m->have_targets = had_targets; return rc; }
+        if (int rc = dg_model_encode_resident(m)) { restore(); return rc; }
+        if (int rc = dg_forward(m, nullptr)) { restore(); return rc; }
         sym_accumulate_kernel<<<m->n, 384, 0, c->stream>>>(m->d_logp, acc, s, s == 0);
         c->launches++;
     }
-    m->have_targets = had_targets;
-    m->forward_done = false;                                   // the staged planes are now those of symmetry 7
+    restore();
+    if (int rc = dg_model_encode_resident(m)) return rc;       // staged planes and labels are the caller's again (they were those of symmetry 7)
     row_argmax_kernel<<<(m->n + 3) / 4, 128, 0, c->stream>>>(acc, m->d_argmax, m->n);
     c->launches++;
     DG_CUDA(cudaGetLastError());

@@ -185,7 +185,8 @@ int dg_argmax(dg_model *m, int32_t *out);
 int dg_eval_batch(dg_model *m, int *errors_out, float *cost_out);
 
 /* c5 inference: 8-fold symmetry-averaged move probabilities for n records (already staged with
- * dg_model_set_batch_raw, sym ignored): probs float[n][361] (may be NULL), argmax int32[n] (may be NULL) */
+ * dg_model_set_batch_raw, sym ignored): probs float[n][361] (may be NULL), argmax int32[n] (may be NULL).  The staged batch
+ * (symmetry ids, planes, labels) is left as the caller staged it. */
 int dg_predict_sym8(dg_model *m, float *probs_out, int32_t *argmax_out);
 
 #ifdef __cplusplus
