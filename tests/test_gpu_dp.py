@@ -1,4 +1,4 @@
-"""-m gpu, needs >= 2 GPUs (skipped otherwise): two ranks, one per GPU, train on the two halves of a batch through
+"""-m gpu, needs >= 2 GPUs (skipped otherwise; the 8-rank case needs 8): the ranks, one per GPU, train on their slices of a batch through
 the library's gradient exchange (NVLink peer memory for the bf16 path, NCCL for fp32) and must end with the parameters
 of one rank training on the whole batch; the gradient vector read back after a step must be the same on both ranks."""
 import os
@@ -39,12 +39,12 @@ dist.destroy_process_group()
 '''
 
 
-@pytest.mark.parametrize("prec", [0, 1])
-def test_two_gpus_match_one(tmp_path, prec):
+@pytest.mark.parametrize("prec,world", [(0, 2), (1, 2), (1, 8)])
+def test_ranks_match_one_gpu(tmp_path, prec, world):
     entry.build()
     from deepgo_b200.host import engine
-    if engine.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+    if engine.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
     g = np.load(os.path.join(entry.ROOT, "tests", "golden", "positions.npz"))
     rng = np.random.default_rng(0)
     ctx = engine.Context(0)
@@ -61,11 +61,13 @@ def test_two_gpus_match_one(tmp_path, prec):
     script = tmp_path / "w.py"
     script.write_text(WORKER)
     env = dict(os.environ, DG_ROOT=entry.ROOT, DG_PARAMS=str(tmp_path / "p.npy"), DG_OUT=str(tmp_path / "out"), DG_PREC=str(prec))
-    subprocess.check_call([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+    subprocess.check_call([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world, "--master-addr", "127.0.0.1",
                            "--master-port", str(port), str(script)], env=env, timeout=300)
-    a = np.load(str(tmp_path / "out") + ".0.npy"); b = np.load(str(tmp_path / "out") + ".1.npy")
-    assert np.array_equal(a, b)                          # replicas stay identical
-    ga = np.load(str(tmp_path / "out") + ".g0.npy"); gb = np.load(str(tmp_path / "out") + ".g1.npy")
-    assert np.array_equal(ga, gb) and np.abs(ga).max() > 0  # the summed gradient of the last step, materialised on demand
+    a = np.load(str(tmp_path / "out") + ".0.npy")
+    ga = np.load(str(tmp_path / "out") + ".g0.npy")
+    assert np.abs(ga).max() > 0
+    for r in range(1, world):
+        assert np.array_equal(a, np.load(str(tmp_path / "out") + ".%d.npy" % r)), r       # replicas stay identical
+        assert np.array_equal(ga, np.load(str(tmp_path / "out") + ".g%d.npy" % r)), r     # the summed gradient of the last step, materialised on demand
     tol = 1e-5 if prec == 0 else 2e-3
     assert np.abs(a - ref).max() < tol

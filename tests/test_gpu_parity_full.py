@@ -1,0 +1,215 @@
+"""-m gpu: the configurations the benchmark numbers are quoted on, compared with the oracle at their own size, and the
+checks that hold the chained tcgen05 kernels tightly (train.lua:4-12 eval, experiments.lua:133-153 model).
+
+  * c2 (12 x 128, batch 128) and c3 (12 x 192, batch 256) against oracle.net.loss_and_grads with the same bf16 rounding
+    points: log-probs 1e-3 * L abs, loss 1e-3 * L, top-1 agreement with the un-rounded fp64 arithmetic >= 90 %, per-tensor
+    gradient cosine > 0.96 and relative error < 2e-1 (hidden ReLU masks that flip between two bf16 forward passes, see
+    test_gpu_net_bf16.py; the next test removes that effect);
+  * a 12 x 128 net built so that every ReLU stays active: no mask can differ between the GPU and the oracle, and the
+    10-layer chain kernels (forward and input gradient) and the multi-layer weight-gradient launch are held to 2e-2
+    relative per tensor;
+  * chained vs per-layer launches (DG_NO_CHAIN=1): the same MMAs in the same order, so log-probs must be BIT-equal and
+    gradients equal up to the order of the L2 reductions (1e-5); default vs DG_DETERMINISTIC=1 likewise;
+  * a He net WITHOUT the +1.0 lift of the last bias: about half of the logits are clamped by the final ReLU
+    (experiments.lua:147); log-probs, loss, top-1 and the head layer's gradient are asserted.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import __graft_entry__ as entry
+from tests import gpu_util as U
+
+pytestmark = pytest.mark.gpu
+
+
+def _model(L, C, n, flat):
+    from deepgo_b200.host import engine
+    m = engine.Model(U.ctx(), L, C, engine.DG_PREC_BF16, max_batch=n)
+    m.set_params(flat.numpy())
+    return m
+
+
+def _grad_report(g, g_q, L, C):
+    from oracle import net
+    errs, cos = [], []
+    for li, ((W, bb, a), (Wq, bq, aq)) in enumerate(zip(net.split_params(g, L, C), net.split_params(g_q, L, C))):
+        errs.append((li, U.rel(W, Wq), U.rel(a, aq), U.rel(bb, bq)))
+        cos.append(float((W.double().flatten() @ Wq.flatten()) / (W.double().norm() * Wq.norm())))
+    return errs, cos
+
+
+def _full_size(golden, L, C, n, seed):
+    from oracle import net
+    b = U.sample(golden, n, seed)
+    x, t = U.oracle_batch(b, np.float32)
+    flat = net.init_params(L, C, seed + 2, "he")
+    net.split_params(flat, L, C)[-1][1].add_(1.0)          # logits kept positive (see test_gpu_net_bf16.py); the clamped case is below
+    xq = torch.from_numpy(x)
+    loss_q, g_q, logp_q = net.loss_and_grads(flat, xq, t, L, C, quant="bf16")
+    logp_r, _ = net.forward(flat, xq, L, C)
+    m = _model(L, C, n, flat)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    logp = m.forward()
+    assert np.isfinite(logp).all()
+    d_q = np.abs(logp - logp_q.numpy()).max()
+    agree = float((logp.argmax(1) == logp_r.numpy().argmax(1)).mean())
+    m.zero_grads()
+    loss = m.loss_backward()
+    g = torch.from_numpy(m.get_grads())
+    errs, cos = _grad_report(g, g_q, L, C)
+    print("full size L=%d C=%d n=%d: max|dlogp| %.3e (vs fp64 %.3e), loss %.6f vs %.6f, top-1 agreement %.3f" %
+          (L, C, n, d_q, np.abs(logp - logp_r.numpy()).max(), loss, loss_q, agree))
+    print("  per-layer relative gradient error (W, a, b):", errs, "cos(W):", cos)
+    assert d_q < 1e-3 * L
+    assert np.abs(logp - logp_r.numpy()).max() < 5e-2
+    assert abs(loss - loss_q) < 1e-3 * L
+    assert agree >= 0.9
+    assert np.array_equal(m.argmax(), logp.argmax(1))
+    assert min(cos) > 0.96, cos
+    assert max(max(e[1:]) for e in errs) < 2e-1, errs
+    # the fused step (graph replay, gradients left in the accumulation buffers) returns the same loss and gradient
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    loss_f = m.train_step(0.0)
+    assert abs(loss_f - loss) < 1e-5
+    assert U.rel(m.get_grads(), g.numpy()) < 1e-4
+
+
+def test_c2_full_batch_vs_oracle(golden):            # BASELINE config 2: the benchmark's own shape and batch
+    _full_size(golden, 12, 128, 128, 41)
+
+
+def test_c3_full_batch_vs_oracle(golden):            # BASELINE config 3: 12 x 192, batch 256 (two N blocks, per-layer launches, SIMT head)
+    _full_size(golden, 12, 192, 256, 43)
+
+
+def always_active_params(L, C, seed):
+    """A net whose ReLUs never clamp, so the GPU and the oracle cannot disagree on a mask: hidden 3x3 weights sum to zero over the
+    input channels for every (output channel, tap), which makes the conv blind to the common offset B of its input, and the
+    conv bias is B = 8 standard deviations of what the conv can produce.  Activations are B + a unit-variance, fully mixed-sign
+    signal; gradients pass through every layer unmasked."""
+    from oracle import net
+    rng = np.random.default_rng(seed)
+    flat = torch.zeros(net.param_count(L, C), dtype=torch.float64)
+    layers = net.split_params(flat, L, C)
+    for i, (W, b, a) in enumerate(layers):
+        co, ci, k, _ = W.shape
+        if i == 0:
+            w = rng.normal(0, np.sqrt(1.0 / 200), W.shape)          # ~8 active planes x 25 taps feed a point
+        else:
+            w = rng.normal(0, np.sqrt(1.0 / (ci * k * k)), W.shape)
+            w -= w.mean(axis=1, keepdims=True)                      # sum over input channels = 0 per (co, ky, kx)
+        if i == L - 1:
+            w *= 1.5
+        W.copy_(torch.from_numpy(w))
+        b.fill_(10.0 if i == L - 1 else 8.0)
+        a.copy_(torch.from_numpy(rng.normal(0, 0.05, a.shape)))
+    return flat
+
+
+def test_chain_kernels_all_relus_active(golden):
+    from oracle import net
+    L, C, n = 12, 128, 16
+    b = U.sample(golden, n, 51)
+    x, t = U.oracle_batch(b, np.float32)
+    flat = always_active_params(L, C, 52)
+    xq = torch.from_numpy(x)
+    logp_q, (hs, zs) = net.forward(flat, xq, L, C, quant="bf16")
+    assert all(float(z.min()) > 0 for z in zs), [float(z.min()) for z in zs]      # the construction holds: nothing is clamped
+    loss_q, g_q, _ = net.loss_and_grads(flat, xq, t, L, C, quant="bf16")
+    m = _model(L, C, n, flat)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    logp = m.forward()
+    m.zero_grads()
+    loss = m.loss_backward()
+    g = torch.from_numpy(m.get_grads())
+    errs, cos = _grad_report(g, g_q, L, C)
+    print("all-active 12x128: max|dlogp| %.3e loss %.6f vs %.6f" % (np.abs(logp - logp_q.numpy()).max(), loss, loss_q))
+    print("  per-layer relative gradient error (W, a, b):", errs, "cos(W):", cos)
+    assert np.abs(logp - logp_q.numpy()).max() < 1e-3 * L
+    assert abs(loss - loss_q) < 1e-3 * L
+    assert max(max(e[1:]) for e in errs) < 2e-2, errs
+    assert min(cos) > 1 - 4e-4, cos
+
+
+WORKER = r'''
+import os, sys, numpy as np
+sys.path.insert(0, os.environ["DG_ROOT"])
+from deepgo_b200.host import engine
+from tests import gpu_util as U
+g = np.load(os.path.join(os.environ["DG_ROOT"], "tests", "golden", "positions.npz"))
+L, C, n = 12, 128, 24
+b = U.sample(g, n, 61)
+flat = np.load(os.environ["DG_PARAMS"])
+ctx = engine.Context(0)
+m = engine.Model(ctx, L, C, engine.DG_PREC_BF16, max_batch=n)
+m.set_params(flat)
+m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+logp = m.forward()
+m.zero_grads(); loss = m.loss_backward()
+grads = m.get_grads()
+m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+loss_f = m.train_step(0.0)
+np.savez(os.environ["DG_OUT"], logp=logp, grads=grads, loss=loss, loss_f=loss_f, grads_f=m.get_grads())
+'''
+
+
+def _run_variant(tmp_path, name, extra_env):
+    script = tmp_path / "variant.py"
+    script.write_text(WORKER)
+    out = str(tmp_path / (name + ".npz"))
+    env = dict(os.environ, DG_ROOT=entry.ROOT, DG_PARAMS=str(tmp_path / "p.npy"), DG_OUT=out, **extra_env)
+    for k in ("DG_NO_CHAIN", "DG_DETERMINISTIC", "DG_NO_GRAPH"):
+        if k not in extra_env:
+            env.pop(k, None)
+    subprocess.check_call([sys.executable, str(script)], env=env, timeout=600, cwd=entry.ROOT)
+    return np.load(out)
+
+
+def test_chain_equals_per_layer_and_deterministic_path(tmp_path):
+    from oracle import net
+    entry.build()
+    flat = net.init_params(12, 128, 62, "he")
+    net.split_params(flat, 12, 128)[-1][1].add_(1.0)
+    np.save(tmp_path / "p.npy", flat.numpy().astype(np.float32))
+    base = _run_variant(tmp_path, "default", {})
+    for name, env in (("nochain", {"DG_NO_CHAIN": "1"}), ("deterministic", {"DG_DETERMINISTIC": "1"}), ("nograph", {"DG_NO_GRAPH": "1"})):
+        v = _run_variant(tmp_path, name, env)
+        # identical MMAs in identical order per accumulator, identical rounding points: the forward pass is bit-equal
+        assert np.array_equal(v["logp"], base["logp"]), name
+        assert float(v["loss"]) == float(base["loss"]), name
+        # gradients: same products, the split-K partial sums meet in a different order
+        assert U.rel(v["grads"], base["grads"]) < 1e-5, name
+        assert U.rel(v["grads_f"], base["grads"]) < 1e-5, name
+        assert abs(float(v["loss_f"]) - float(base["loss"])) < 1e-6, name
+
+
+def test_clamped_logits_final_relu(golden):
+    """He weights as they are: the final ReLU (experiments.lua:147) clamps about half of the logits on the bf16 path."""
+    from oracle import net
+    L, C, n = 6, 128, 32
+    b = U.sample(golden, n, 71)
+    x, t = U.oracle_batch(b, np.float32)
+    flat = net.init_params(L, C, 72, "he")
+    xq = torch.from_numpy(x)
+    loss_q, g_q, logp_q = net.loss_and_grads(flat, xq, t, L, C, quant="bf16")
+    _, (hs, zs) = net.forward(flat, xq, L, C, quant="bf16")
+    clamped = float((zs[-1] <= 0).double().mean())
+    assert 0.1 < clamped < 0.9, clamped                  # the case is real: a good share of the logits sits at the clamp
+    m = _model(L, C, n, flat)
+    m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    logp = m.forward()
+    assert np.abs(logp - logp_q.numpy()).max() < 1e-3 * L
+    m.zero_grads()
+    loss = m.loss_backward()
+    assert abs(loss - loss_q) < 1e-3 * L
+    g = torch.from_numpy(m.get_grads())
+    (Wh, bh, ah), (Wq, bq, aq) = net.split_params(g, L, C)[-1], net.split_params(g_q, L, C)[-1]
+    print("clamped fraction %.3f, head gradient errors:" % clamped, U.rel(Wh, Wq), U.rel(ah, aq), U.rel(bh, bq))
+    # a logit that sits within bf16 noise of zero may be clamped on one side only: each such point moves the head's
+    # gradient by about 1/361 of its norm
+    assert U.rel(Wh, Wq) < 5e-2 and U.rel(ah, aq) < 5e-2

@@ -86,6 +86,31 @@ def test_load_minibatch_matches_oracle(host, golden):
 
 
 @pytest.mark.gpu
+def test_queued_minibatches_load_concurrently_and_match_oracle(host, tmp_path):
+    """data.lua:82-96: many minibatches queued at once on the loader pool (train() queues all its iterations up front).  Every
+    callback must see the planes of ITS files -- different batch sizes, so a shared staging buffer that is re-grown or
+    overwritten by another job would show."""
+    from oracle import encode
+    d, dl = host["data"], host["dataloader"]
+    root = _make_tree(tmp_path)
+    ds = d.Dataset(root=str(root / "data"), directory="test")
+    got = []
+    import random
+    random.seed(3)
+    sizes = [1, 7, 2, 33, 5, 64, 3, 12] * 3
+    for n in sizes:
+        d.queue_on_minibatch(got.append, ds, n, str(root))
+    d.do_queued_tasks()
+    assert [len(mb["records"]) for mb in got] == sizes
+    for mb in got:
+        assert mb["input"].shape == (len(mb["records"]), 37, 19, 19)
+        for k, r in enumerate(mb["records"]):
+            pl = r["move"]["player"]
+            assert np.array_equal(mb["input"][k], encode.preprocess(r["input"], pl, r["ranks"][pl]).astype(np.float32))
+            assert mb["output"][k] == 19 * (r["move"]["x"] - 1) + r["move"]["y"]
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("precision", [0, 1])
 def test_localtest_replay(host, tmp_path, capsys, precision):
     """localtest.lua: basicGoExperiment (3 layers x 64), batchSize 2, validation_interval 20, iters 20."""
