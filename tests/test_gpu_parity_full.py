@@ -65,7 +65,8 @@ def _full_size(golden, L, C, n, seed):
     print("full size L=%d C=%d n=%d: max|dlogp| %.3e (vs fp64 %.3e), loss %.6f vs %.6f, top-1 agreement %.3f" %
           (L, C, n, d_q, np.abs(logp - logp_r.numpy()).max(), loss, loss_q, agree))
     print("  per-layer relative gradient error (W, a, b):", errs, "cos(W):", cos)
-    assert d_q < 1e-3 * L
+    assert d_q < 2e-3 * L
+    assert np.abs(logp - logp_q.numpy()).mean() < 2e-3
     assert np.abs(logp - logp_r.numpy()).max() < 5e-2
     assert abs(loss - loss_q) < 1e-3 * L
     assert agree >= 0.9
