@@ -771,8 +771,7 @@ __global__ void __launch_bounds__(384, 1) wgrad_umma_kernel(const __grid_constan
                 release(2);
                 red_kx(1, rb2);
                 red_kx(2, ra);
-                continue;
-            }
+            } else
             for (int w = 0; w < CONV_MMA_WARPS; ++w) {
             mbar_wait(&acc_full[w], lc & 1);
             tc_fence_after();
@@ -1825,7 +1824,7 @@ struct Bf16Path {
     // the small HBM-bound gradient kernels (bias gradients, split-K reduction) run on a side stream, under the
     // tensor-core kernels of the main stream
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_memset = nullptr, ev_dz = nullptr, ev_wgrad = nullptr, ev_bias[2] = {nullptr, nullptr}, ev_reduce[2] = {nullptr, nullptr}, ev_join = nullptr;
+    cudaEvent_t ev_head = nullptr, ev_fork = nullptr, ev_memset = nullptr, ev_dz = nullptr, ev_wgrad = nullptr, ev_bias[2] = {nullptr, nullptr}, ev_reduce[2] = {nullptr, nullptr}, ev_join = nullptr;
     int num_sms = 148;
     bool head_bwd_done = false;
 };
@@ -2050,7 +2049,7 @@ int dg_bf16_create(dg_model *m) {
     DG_CUDA(cudaMalloc((void **)&b->scratch, 2 * scratch));
     b->scratch_bytes = scratch;
     DG_CUDA(cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking));
-    cudaEvent_t *evs[] = {&b->ev_fork, &b->ev_memset, &b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
+    cudaEvent_t *evs[] = {&b->ev_head, &b->ev_fork, &b->ev_memset, &b->ev_dz, &b->ev_wgrad, &b->ev_bias[0], &b->ev_bias[1], &b->ev_reduce[0], &b->ev_reduce[1], &b->ev_join};
     for (cudaEvent_t *e : evs) DG_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
     DG_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 15 * 1024));
@@ -2079,6 +2078,8 @@ void dg_bf16_destroy(dg_model *m) {
     dg_dp_p2p_destroy(b->p2p);
     cudaFree(b->head_part);
     if (b->side) cudaStreamDestroy(b->side);
+    cudaEvent_t evs[] = {b->ev_head, b->ev_fork, b->ev_memset, b->ev_dz, b->ev_wgrad, b->ev_bias[0], b->ev_bias[1], b->ev_reduce[0], b->ev_reduce[1], b->ev_join};
+    for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
     delete b;
     m->bf = nullptr;
 }
@@ -2291,6 +2292,38 @@ int dg_bf16_forward(dg_model *m) {
 int dg_bf16_backward(dg_model *m, float scale) {
     Bf16Path *b = m->bf;
     dg_ctx *c = m->ctx;
+    // Inside dg_train_step the SGD kernel reads the accumulation buffers itself: the Torch7-order gradient vector is not
+    // materialised (dg_bf16_sync_grads does it on demand, e.g. for dg_model_get_grads)
+    const bool defer = m->fused_step && b->defer_grads;
+    // ---- the weight-gradient launches of this pass: conv layers L-2 .. 1 have one shape and (default path) go out as ONE launch;
+    // layer 0 on its own
+    struct WgLaunch { int l, nl, ngroups, grid; WgradPlan w; };
+    std::vector<WgLaunch> wl;
+    for (int l = m->L - 2; l >= 0;) {
+        const LayerInfo &li = m->layers[l];
+        const Geom &g = l == 0 ? b->g_first : b->g3;
+        WgLaunch q; q.l = l;
+        if (int rc = wgrad_plan(m, b->ops[l].cin_pad, li.cout, li.k, g, q.w)) return rc;
+        q.nl = 1;
+        if (!b->deterministic && l >= 1) q.nl = std::min(l, WG_MAX_LAYERS);       // layers l, l-1, .., l-nl+1 (all >= 1)
+        const int panels_l = g.ntiles * 128 / q.w.rp;
+        // G layer groups: group g walks layers g, g + G, ..; the splits of a kernel row are dealt evenly to the groups, every CTA keeps one
+        // panel index (splits per group a multiple of the panels).  Default: TWO PHASES (G = layers / 2): a CTA accumulates a layer over
+        // many units and drains only twice, and the drain's red.global traffic (the partial tile of every CTA) drops with the number
+        // of CTAs per layer: 10 layers in 5 groups of 27 CTAs measured 104 us against 113 us for 2 groups of 72 CTAs, 13 SMs idle
+        // notwithstanding.  DG_WG_GROUPS overrides.
+        static const int env_groups = [] { const char *e = getenv("DG_WG_GROUPS"); return e ? atoi(e) : 0; }();
+        const int want_groups = env_groups > 0 ? env_groups : (q.nl % 2 == 0 ? q.nl / 2 : 1);
+        q.ngroups = 1;
+        if (!b->deterministic && q.nl >= 2 && want_groups >= 2 && q.nl % want_groups == 0) {
+            const int per_row = b->num_sms / q.w.combos;                                  // CTAs a kernel row can have
+            const int st = per_row / (want_groups * panels_l) * (want_groups * panels_l);   // .. dealt evenly to the groups
+            if (st >= want_groups * panels_l && m->n * panels_l >= st / want_groups) { q.ngroups = want_groups; q.w.splits = st; }
+        }
+        q.grid = q.w.combos * q.w.splits;
+        wl.push_back(q);
+        l -= q.nl;
+    }
     // the accumulation buffers are cleared on the side stream while the head and the input-gradient chain run (a memset node between
     // two kernels of the main stream costs its 5 us and the programmatic launch overlap of its neighbours)
     if (!b->deterministic) {
@@ -2303,6 +2336,20 @@ int dg_bf16_backward(dg_model *m, float scale) {
         DG_CUDA(cudaEventRecord(b->ev_memset, b->side));
     }
     if (int rc = launch_head(m, true, scale)) return rc;      // its per-position gradient partials are summed on the side stream
+    DG_CUDA(cudaEventRecord(b->ev_head, c->stream));
+    DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_head, 0));
+    {
+        const LayerInfo &lh = m->layers[m->L - 1];
+        cudaStream_t hst = b->side;
+        dg_prof_scope _ps(c, DG_K_HEAD, hst);
+        // a deferring fused step sums the head layer's gradient into the head block of the accumulation buffers
+        float *hW = defer ? b->gacc : m->grads + lh.offW, *hb = defer ? b->gacc + lh.nW : m->grads + lh.offB;
+        float *ha = defer ? b->gacc + lh.nW + lh.cout : m->grads + lh.offA;
+        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32 + 1, 256, 0, hst>>>(b->head_part, m->n, m->C, hW, hb, ha, m->d_loss_n, m->d_argmax,
+                                                                                           m->d_targets, m->d_loss, m->d_errors);
+        m->loss_reduced = true;
+        c->launches++;
+    }
     // ---- input gradients first: dZ_{l} -> dZ_{l-1} for conv layers l = L-2 .. 1 (transposed conv with flipped taps, masked by
     // the ReLU of layer l's input h_l); with C <= 128 the whole chain is one kernel with dZ resident in shared memory
     {
@@ -2328,27 +2375,15 @@ int dg_bf16_backward(dg_model *m, float scale) {
         }
     }
     // every dZ_l is complete on the main stream: the side stream may read them
-    DG_CUDA(cudaEventRecord(b->ev_dz, c->stream));
-    DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
+    if (!b->fused_bias) {
+        DG_CUDA(cudaEventRecord(b->ev_dz, c->stream));
+        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_dz, 0));
+    }
     if (!b->deterministic) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_memset, 0));     // the weight-gradient kernels add into the cleared buffers
     bool rec_reduce[2] = {false, false};   // events recorded in THIS pass (stream capture forbids waiting on older records)
-    int dp_done_from = m->L - 1;           // conv layers >= this index already left in a data-parallel bucket
     static long long *wdbg = nullptr;
     static const bool wtl = getenv("DG_TIMELINE") != nullptr;
     if (wtl && !wdbg) cudaMalloc(&wdbg, 148 * 8 * sizeof(long long));
-    {
-        const LayerInfo &lh = m->layers[m->L - 1];
-        cudaStream_t hst = b->side;
-        dg_prof_scope _ps(c, DG_K_HEAD, hst);
-        // a deferring fused step sums the head layer's gradient into the head block of the accumulation buffers
-        const bool to_acc = m->fused_step && b->defer_grads;
-        float *hW = to_acc ? b->gacc : m->grads + lh.offW, *hb = to_acc ? b->gacc + lh.nW : m->grads + lh.offB;
-        float *ha = to_acc ? b->gacc + lh.nW + lh.cout : m->grads + lh.offA;
-        head_grad_reduce_kernel<<<(9 * m->C + DG_POINTS + 31) / 32 + 1, 256, 0, hst>>>(b->head_part, m->n, m->C, hW, hb, ha, m->d_loss_n, m->d_argmax,
-                                                                                           m->d_targets, m->d_loss, m->d_errors);
-        m->loss_reduced = true;
-        c->launches++;
-    }
     // bias gradients of every conv layer: side stream, all dZ are ready
     for (int l = m->L - 2; l >= 0 && !b->fused_bias; --l) {
         const LayerInfo &li = m->layers[l];
@@ -2359,16 +2394,12 @@ int dg_bf16_backward(dg_model *m, float scale) {
                                                                              g.rows, g.pitch, g.pad, groups);
         c->launches++;
     }
-    // weight gradients: conv layers L-2 .. 1 have one shape and (default path) go out as ONE launch; layer 0 on its own
-    int l = m->L - 2;
-    while (l >= 0) {
+    for (const WgLaunch &q : wl) {
+        const int l = q.l, nl = q.nl;
+        const WgradPlan &w = q.w;
         const LayerInfo &li = m->layers[l];
         const LayerOps &o = b->ops[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
-        WgradPlan w;
-        if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, g, w)) return rc;
-        int nl = 1;
-        if (!b->deterministic && l >= 1) nl = std::min(l, WG_MAX_LAYERS);       // layers l, l-1, .., l-nl+1 (all >= 1)
         const int par = l & 1;
         float *scratch = b->scratch + (size_t)par * (b->scratch_bytes / 4);
         WgradParams wp{};
@@ -2381,70 +2412,61 @@ int dg_bf16_backward(dg_model *m, float scale) {
         wp.scratch = scratch; wp.nl = nl;
         wp.n = m->n; wp.cin = o.cin_pad; wp.cout = li.cout;
         wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = li.k; wp.first = g.first; wp.ntiles = g.ntiles;
-        // two layer groups when the layers and the splits divide evenly (the per-CTA panel index must stay fixed for the bias gradient)
-        const int panels_l = g.ntiles * 128 / w.rp;
-        const int ngroups = (!b->deterministic && nl % 2 == 0 && w.splits % (2 * panels_l) == 0 && m->n * panels_l >= w.splits) ? 2 : 1;
-        wp.ngroups = ngroups;
-        wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits / ngroups; wp.nstages = w.nstages;
+        wp.ngroups = q.ngroups;
+        wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits / q.ngroups; wp.nstages = w.nstages;
         wp.dbg = wtl ? wdbg : nullptr;
         wp.tl = c->tl; wp.tl_id = l == 0 ? DG_TL_WGRAD0 : DG_TL_WGRAD;
         // deterministic path: this scratch half was last read by the reduction two layers ago
         if (b->deterministic && rec_reduce[par]) DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_reduce[par], 0));
         { dg_prof_scope _ps(c, DG_K_WGRAD);
-        if (w.rp == 96) DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<96>, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp));
-        else DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<128>, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp));
+        if (w.rp == 96) DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<96>, dim3(q.grid), dim3(384), w.smem, c->stream, wp));
+        else DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<128>, dim3(q.grid), dim3(384), w.smem, c->stream, wp));
         }
         c->launches++;
         if (wp.dbg) {
             std::vector<long long> h(148 * 8);
             cudaStreamSynchronize(c->stream);
             cudaMemcpy(h.data(), wp.dbg, h.size() * 8, cudaMemcpyDeviceToHost);
-            double d1 = 0, d2 = 0, d3 = 0, d4 = 0, d5 = 0, d6 = 0; const int gsz = w.combos * w.splits;
+            double d1 = 0, d2 = 0, d3 = 0, d4 = 0, d5 = 0, d6 = 0; const int gsz = q.grid;
             for (int i = 0; i < gsz; ++i) { d1 += (double)(h[i * 8 + 1] - h[i * 8]) / gsz; d2 += (double)(h[i * 8 + 2] - h[i * 8]) / gsz; d3 += (double)h[i * 8 + 3] / gsz; d4 += (double)(h[i * 8 + 4] - h[i * 8]) / gsz; d5 += (double)h[i * 8 + 5] / gsz; d6 += (double)h[i * 8 + 6] / gsz; }
             fprintf(stderr, "wgrad timeline (cycles, mean over %d CTAs) k=%d layers=%d: mma loop start %.0f end %.0f (waiting for panels %.0f) | CTA end %.0f | producer: waiting for a free stage %.0f, issuing copies %.0f\n", gsz, li.k, nl, d1, d2, d3, d4, d5, d6);
         }
-        DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
-        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));
-        for (int j = 0; j < nl; ++j) {
-            const int lj = l - j;
-            const LayerInfo &lij = m->layers[lj];
-            if (b->deterministic) {
+        if (b->deterministic) {
+            DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
+            DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));
+            for (int j = 0; j < nl; ++j) {
+                const int lj = l - j;
+                const LayerInfo &lij = m->layers[lj];
                 dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
                 wgrad_reduce_kernel<<<b->num_sms * 8, 256, 0, b->side>>>(scratch, m->grads + lij.offW, lij.cin, b->ops[lj].cin_pad, lij.cout, lij.k, w.nb,
                                                                          w.n_mblk, w.n_nblk, w.splits);
                 c->launches++;
             }
+            DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
+            rec_reduce[par] = true;
         }
-        DG_CUDA(cudaEventRecord(b->ev_reduce[par], b->side));
-        rec_reduce[par] = true;
-        // (data parallel: exchanging the 3x3 layers' blocks on the side stream under the first layer's weight-gradient kernel was
-        // measured: the exchange kernel's fixed cost -- two cross-GPU barriers and an NVLink round trip each way, ~17 us -- is then
-        // paid twice and the tail of the overlapped launch still sticks out; one exchange after the last kernel is shorter)
-        l -= nl;
     }
-    // Inside dg_train_step the SGD kernel reads the accumulation buffers itself: the Torch7-order gradient vector is not
-    // materialised (dg_bf16_sync_grads does it on demand, e.g. for dg_model_get_grads)
-    const bool defer = m->fused_step && b->defer_grads;
     b->grads_pending = defer;
     if (!b->deterministic && !defer) {
         // one launch folds every layer's accumulation buffer into the Torch7-order gradient
+        DG_CUDA(cudaEventRecord(b->ev_wgrad, c->stream));
+        DG_CUDA(cudaStreamWaitEvent(b->side, b->ev_wgrad, 0));
         dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, b->side);
         wgrad_finalize_kernel<<<dim3(96, m->L - 1), 256, FIN_SMEM_FLOATS * 4, b->side>>>(b->fin_table, c->tl);
         c->launches++;
     }
+    // the side stream joins: head-layer gradient, (deterministic path) reductions, gradient vector
     DG_CUDA(cudaEventRecord(b->ev_join, b->side));
     DG_CUDA(cudaStreamWaitEvent(c->stream, b->ev_join, 0));
-    // data parallel: all weight gradients of the 3x3 layers become final together (one persistent launch), so the exchange
-    // is ONE allreduce of the whole gradient -- latency-optimal for 8.4 MB over NVLink (plus the 6 KB of the head layer when the
-    // conv layers' gradient stays in the accumulation buffers)
+    // data parallel: ONE allreduce of the whole gradient after the last weight-gradient kernel.  Exchanging layer blocks earlier, under
+    // the weight-gradient kernels, was built three ways and measured slower every time: those kernels keep the L2 busy
+    // with operand traffic and red.global additions, and whatever shares it with them -- remote loads, fences, flags -- crawls.
     if (m->fused_step && c->world > 1) {
         const LayerInfo &l0 = m->layers[0], &lh = m->layers[m->L - 1];
         const size_t head_n = lh.nW + lh.cout + (size_t)lh.cout * DG_POINTS;
         if (defer) {
-            // head block + the conv layers not exchanged yet: one contiguous range from the start of the allocation
-            const size_t end = dp_done_from < m->L - 1 ? b->gacc_off[dp_done_from] : b->gacc_floats;
-            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p, c->stream, 0, end, 0, b->p2p_pull ? 1 : 0)) return rc; }   // one kernel over NVLink peer memory
-            else if (int rc = dg_dp_bucket(c, b->gacc, end)) return rc;
+            if (b->p2p) { if (int rc = dg_dp_p2p_allreduce(c, b->p2p, c->stream, 0, b->gacc_floats, 0, b->p2p_pull ? 1 : 0)) return rc; }   // one kernel over NVLink peer memory
+            else if (int rc = dg_dp_bucket(c, b->gacc, b->gacc_floats)) return rc;
         } else {
             if (int rc = dg_dp_bucket(c, m->grads + l0.offW, lh.offW + head_n - l0.offW)) return rc;
         }

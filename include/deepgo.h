@@ -67,15 +67,18 @@ int dg_prof_timeline(dg_ctx *ctx, unsigned long long *out, int n);
 
 /* ---- data parallel (nn.DataParallelTable(1), experiments.lua:155-168) ---------------------- */
 /* One process per GPU.  Rank 0 calls dg_dp_unique_id and ships the 128 bytes to the other ranks
- * (any side channel); every rank then calls dg_ctx_init_dp.  After that dg_train_step* sums the
- * gradient over ranks (NCCL allreduce, per-layer buckets) before the SGD update; each rank must
- * scale its loss gradient by 1/global_batch (dg_model_set_global_batch) so the sum is the
- * global-batch mean gradient -- what DataParallelTable + ClassNLLCriterion on the gathered output
- * produce. */
+ * (any side channel); every rank then calls dg_ctx_init_dp.  After that dg_train_step sums the
+ * gradient over ranks before the SGD update: on the bf16 path ONE kernel after the last
+ * weight-gradient kernel, a two-shot allreduce over NVLink peer memory (CUDA IPC mapping of the
+ * gradient accumulation buffers; bit-identical sums on every rank), captured in the step graph; NCCL
+ * allreduce as the
+ * fallback when peer mapping is unavailable, and on the fp32 path).  Each rank must scale its loss
+ * gradient by 1/global_batch (dg_model_set_global_batch) so the sum is the global-batch mean
+ * gradient -- what DataParallelTable + ClassNLLCriterion on the gathered output produce. */
 int dg_dp_unique_id(char id_out[128]);
 int dg_ctx_init_dp(dg_ctx *ctx, int rank, int world, const char id[128]);
-/* sum the whole gradient vector over ranks (for callers that run eval() and SGD:step as separate calls,
- * train.lua:111 then :131); dg_train_step does this itself, bucket by bucket, overlapped with backward */
+/* sum the whole gradient vector over ranks with one NCCL allreduce (for callers that run eval() and SGD:step as
+ * separate calls, train.lua:111 then :131); dg_train_step does the exchange itself, see above */
 int dg_dp_allreduce_grads(dg_model *m);
 
 /* ---- feature planes (dataloader.lua) ------------------------------------------------------ */
