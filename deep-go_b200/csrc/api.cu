@@ -9,6 +9,24 @@
 
 static thread_local char g_err[1024] = "";
 
+// multi.cu: one process, several devices
+int dgm_ctx_destroy_kids(dg_ctx *c);
+int dgm_ctx_synchronize(dg_ctx *c);
+int dgm_model_create(dg_ctx *c, int num_layers, int channel_size, int in_planes, int k_first, int precision, int max_batch, dg_model **out);
+int dgm_model_destroy(dg_model *m);
+int dgm_set_params(dg_model *m, const float *host, size_t n);
+int dgm_zero_grads(dg_model *m);
+int dgm_set_batch_raw(dg_model *m, const uint8_t *raw, const uint8_t *player, const uint8_t *rank, const uint8_t *sym, const uint8_t *x, const uint8_t *y, int n);
+int dgm_set_batch_planes(dg_model *m, const float *planes, const int32_t *targets0, int n);
+int dgm_encode_resident(dg_model *m);
+int dgm_forward(dg_model *m, float *logprobs_out);
+int dgm_argmax(dg_model *m, int32_t *out);
+int dgm_eval_batch(dg_model *m, int *errors_out, float *cost_out);
+int dgm_loss_backward(dg_model *m, float *loss_out);
+int dgm_sgd_step(dg_model *m, float rate);
+int dgm_train_step(dg_model *m, float rate, float *loss_out);
+#define DG_MULTI(m) (!(m)->kids.empty())
+
 void dg_set_error(const char *fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -55,6 +73,7 @@ extern "C" int dg_ctx_create(int device, dg_ctx **out) {
 extern "C" int dg_ctx_destroy(dg_ctx *c) {
     if (!c) return 0;
     if (c->live_models > 0) { c->zombie = true; return 0; }   // a model still uses this context: free it with the last model
+    if (!c->kids.empty()) dgm_ctx_destroy_kids(c);
     cudaSetDevice(c->dev);
     cudaStreamSynchronize(c->stream);
     if (c->scratch) cudaFree(c->scratch);
@@ -68,6 +87,7 @@ extern "C" int dg_ctx_destroy(dg_ctx *c) {
 
 extern "C" int dg_ctx_synchronize(dg_ctx *c) {
     DG_REQUIRE(c, "dg_ctx_synchronize: ctx is NULL");
+    if (!c->kids.empty()) return dgm_ctx_synchronize(c);
     DG_CUDA(cudaStreamSynchronize(c->stream));
     return 0;
 }
@@ -75,16 +95,25 @@ extern "C" int dg_ctx_synchronize(dg_ctx *c) {
 extern "C" int dg_ctx_launch_count(dg_ctx *c, long long *out) {
     DG_REQUIRE(c && out, "dg_ctx_launch_count: NULL argument");
     *out = c->launches;
+    for (dg_ctx *k : c->kids) *out += k->launches;
     return 0;
 }
 
 extern "C" int dg_timer_start(dg_ctx *c) {
     DG_REQUIRE(c, "dg_timer_start: ctx is NULL");
+    if (c->kids.empty()) DG_CUDA(cudaSetDevice(c->dev));
+    if (!c->kids.empty()) { for (dg_ctx *k : c->kids) if (int rc = dg_timer_start(k)) return rc; return 0; }
     DG_CUDA(cudaEventRecord(c->t0, c->stream));
     return 0;
 }
 extern "C" int dg_timer_stop(dg_ctx *c, float *ms) {
     DG_REQUIRE(c && ms, "dg_timer_stop: NULL argument");
+    if (!c->kids.empty()) {                          // the slowest device
+        *ms = 0.f;
+        for (dg_ctx *k : c->kids) { float t = 0.f; if (int rc = dg_timer_stop(k, &t)) return rc; if (t > *ms) *ms = t; }
+        return 0;
+    }
+    DG_CUDA(cudaSetDevice(c->dev));
     DG_CUDA(cudaEventRecord(c->t1, c->stream));
     DG_CUDA(cudaEventSynchronize(c->t1));
     DG_CUDA(cudaEventElapsedTime(ms, c->t0, c->t1));
@@ -131,6 +160,7 @@ extern "C" int dg_prof_timeline(dg_ctx *c, unsigned long long *out, int n) {
 
 extern "C" int dg_ctx_flush_l2(dg_ctx *c) {
     DG_REQUIRE(c, "dg_ctx_flush_l2: ctx is NULL");
+    if (!c->kids.empty()) { for (dg_ctx *k : c->kids) if (int rc = dg_ctx_flush_l2(k)) return rc; return 0; }
     DG_CUDA(cudaSetDevice(c->dev));
     if (!c->flush_buf) {
         c->flush_bytes = (size_t)256 << 20;       // > 126 MB L2
@@ -213,20 +243,12 @@ extern "C" int dg_encode_labels(const uint8_t *x, const uint8_t *y, const uint8_
 // ---------------------------------------------------------------------------------------------
 // model
 // ---------------------------------------------------------------------------------------------
-extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int in_planes, int k_first, int precision,
-                               int max_batch, dg_model **out) {
-    DG_REQUIRE(c && out, "dg_model_create: NULL argument");
-    DG_REQUIRE(num_layers >= 2, "dg_model_create: numLayers must be >= 2");
-    DG_REQUIRE(channel_size >= 1 && max_batch >= 1, "dg_model_create: bad channelSize/max_batch");
-    DG_REQUIRE(k_first == 3 || k_first == 5, "dg_model_create: first kernel must be 3 or 5");
-    DG_REQUIRE(in_planes == DG_PLANES, "dg_model_create: in_planes must be %d (dataloader.lua TOTAL)", DG_PLANES);
-    DG_REQUIRE(precision == DG_PREC_FP32 || precision == DG_PREC_BF16, "dg_model_create: unknown precision %d", precision);
-    DG_CUDA(cudaSetDevice(c->dev));
-    dg_model *m = new dg_model();
-    m->ctx = c; m->L = num_layers; m->C = channel_size; m->in_planes = in_planes; m->k_first = k_first;
-    m->prec = precision; m->max_batch = max_batch;
+// layer table and flat-vector offsets (experiments.lua:88-93,105-107)
+int dg_model_layout(dg_model *m, int num_layers, int channel_size, int in_planes, int k_first) {
+    m->L = num_layers; m->C = channel_size; m->in_planes = in_planes; m->k_first = k_first;
+    m->layers.clear();
     size_t off = 0;
-    for (int l = 0; l < num_layers; ++l) {               // experiments.lua:88-93
+    for (int l = 0; l < num_layers; ++l) {
         LayerInfo li;
         li.cin = l == 0 ? in_planes : channel_size;
         li.cout = l == num_layers - 1 ? 1 : channel_size;
@@ -238,6 +260,23 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
         m->layers.push_back(li);
     }
     m->P = off;
+    return 0;
+}
+
+extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int in_planes, int k_first, int precision,
+                               int max_batch, dg_model **out) {
+    DG_REQUIRE(c && out, "dg_model_create: NULL argument");
+    DG_REQUIRE(num_layers >= 2, "dg_model_create: numLayers must be >= 2");
+    DG_REQUIRE(channel_size >= 1 && max_batch >= 1, "dg_model_create: bad channelSize/max_batch");
+    DG_REQUIRE(k_first == 3 || k_first == 5, "dg_model_create: first kernel must be 3 or 5");
+    DG_REQUIRE(in_planes == DG_PLANES, "dg_model_create: in_planes must be %d (dataloader.lua TOTAL)", DG_PLANES);
+    DG_REQUIRE(precision == DG_PREC_FP32 || precision == DG_PREC_BF16, "dg_model_create: unknown precision %d", precision);
+    if (!c->kids.empty()) return dgm_model_create(c, num_layers, channel_size, in_planes, k_first, precision, max_batch, out);
+    DG_CUDA(cudaSetDevice(c->dev));
+    dg_model *m = new dg_model();
+    m->ctx = c; m->L = num_layers; m->C = channel_size; m->in_planes = in_planes; m->k_first = k_first;
+    m->prec = precision; m->max_batch = max_batch;
+    if (int rc = dg_model_layout(m, num_layers, channel_size, in_planes, k_first)) return rc;
     c->live_models++;
     const size_t B = max_batch;
     DG_CUDA(cudaMalloc(&m->params, m->P * 4));
@@ -270,6 +309,7 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
 
 extern "C" int dg_model_destroy(dg_model *m) {
     if (!m) return 0;
+    if (DG_MULTI(m)) return dgm_model_destroy(m);
     cudaSetDevice(m->ctx->dev);
     cudaStreamSynchronize(m->ctx->stream);
     if (m->bf) dg_bf16_destroy(m);
@@ -296,6 +336,7 @@ extern "C" int dg_model_param_count(dg_model *m, size_t *out) {
 extern "C" int dg_model_set_params(dg_model *m, const float *host, size_t n) {
     DG_REQUIRE(m && host, "dg_model_set_params: NULL argument");
     DG_REQUIRE(n == m->P, "dg_model_set_params: got %zu values, the model has %zu parameters", n, m->P);
+    if (DG_MULTI(m)) return dgm_set_params(m, host, n);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     DG_CUDA(cudaMemcpyAsync(m->params, host, n * 4, cudaMemcpyHostToDevice, m->ctx->stream));
     if (m->bf) if (int rc = dg_bf16_params_changed(m)) return rc;
@@ -305,6 +346,7 @@ extern "C" int dg_model_set_params(dg_model *m, const float *host, size_t n) {
 extern "C" int dg_model_get_params(dg_model *m, float *host, size_t n) {
     DG_REQUIRE(m && host, "dg_model_get_params: NULL argument");
     DG_REQUIRE(n == m->P, "dg_model_get_params: buffer holds %zu values, the model has %zu parameters", n, m->P);
+    if (DG_MULTI(m)) return dg_model_get_params(m->kids[0], host, n);        // the replicas are identical
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     DG_CUDA(cudaMemcpyAsync(host, m->params, n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
     DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
@@ -313,6 +355,7 @@ extern "C" int dg_model_get_params(dg_model *m, float *host, size_t n) {
 extern "C" int dg_model_get_grads(dg_model *m, float *host, size_t n) {
     DG_REQUIRE(m && host, "dg_model_get_grads: NULL argument");
     DG_REQUIRE(n == m->P, "dg_model_get_grads: buffer holds %zu values, the model has %zu parameters", n, m->P);
+    if (DG_MULTI(m)) return dg_model_get_grads(m->kids[0], host, n);         // every replica holds the summed gradient
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (m->bf) if (int rc = dg_bf16_sync_grads(m)) return rc;
     DG_CUDA(cudaMemcpyAsync(host, m->grads, n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
@@ -321,6 +364,7 @@ extern "C" int dg_model_get_grads(dg_model *m, float *host, size_t n) {
 }
 extern "C" int dg_zero_grads(dg_model *m) {
     DG_REQUIRE(m, "dg_zero_grads: model is NULL");
+    if (DG_MULTI(m)) return dgm_zero_grads(m);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (m->bf) dg_bf16_drop_pending_grads(m);
     DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, m->ctx->stream));
@@ -328,6 +372,7 @@ extern "C" int dg_zero_grads(dg_model *m) {
 }
 extern "C" int dg_model_set_global_batch(dg_model *m, int gb) {
     DG_REQUIRE(m && gb >= 0, "dg_model_set_global_batch: bad argument");
+    if (DG_MULTI(m)) { m->global_batch = gb; return 0; }                      // handed to the replicas when a batch is staged
     if (gb != m->global_batch && m->step_graph) {
         // the captured step holds 1/global_batch as a by-value kernel argument: capture again
         DG_CUDA(cudaSetDevice(m->ctx->dev));
@@ -341,6 +386,11 @@ extern "C" int dg_model_set_global_batch(dg_model *m, int gb) {
 extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uint8_t *player, const uint8_t *rank,
                                       const uint8_t *sym, const uint8_t *x, const uint8_t *y, int n) {
     DG_REQUIRE(m, "dg_model_set_batch_raw: model is NULL");
+    if (DG_MULTI(m)) {
+        DG_REQUIRE(raw && player && rank, "dg_model_set_batch_raw: NULL buffer");
+        DG_REQUIRE((x == nullptr) == (y == nullptr), "dg_model_set_batch_raw: x and y must both be given or both NULL");
+        return dgm_set_batch_raw(m, raw, player, rank, sym, x, y, n);
+    }
     DG_REQUIRE(n >= 1 && n <= m->max_batch, "dg_model_set_batch_raw: batch %d outside 1..%d", n, m->max_batch);
     DG_REQUIRE(raw && player && rank, "dg_model_set_batch_raw: NULL buffer");
     DG_REQUIRE((x == nullptr) == (y == nullptr), "dg_model_set_batch_raw: x and y must both be given or both NULL");
@@ -381,6 +431,7 @@ extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uin
 
 extern "C" int dg_model_encode_resident(dg_model *m) {
     DG_REQUIRE(m, "dg_model_encode_resident: model is NULL");
+    if (DG_MULTI(m)) return dgm_encode_resident(m);
     DG_REQUIRE(m->have_raw && m->n > 0, "dg_model_encode_resident: no raw records staged (dg_model_set_batch_raw)");
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
@@ -392,6 +443,7 @@ extern "C" int dg_model_encode_resident(dg_model *m) {
 
 extern "C" int dg_model_set_batch_planes(dg_model *m, const float *planes, const int32_t *targets0, int n) {
     DG_REQUIRE(m && planes, "dg_model_set_batch_planes: NULL argument");
+    if (DG_MULTI(m)) return dgm_set_batch_planes(m, planes, targets0, n);
     DG_REQUIRE(n >= 1 && n <= m->max_batch, "dg_model_set_batch_planes: batch %d outside 1..%d", n, m->max_batch);
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
@@ -409,7 +461,7 @@ extern "C" int dg_model_set_batch_planes(dg_model *m, const float *planes, const
 static float grad_scale(dg_model *m) { return 1.0f / (float)(m->global_batch > 0 ? m->global_batch : m->n); }
 
 // forward up to the ReLU'd last-layer map, then log-softmax (+ per-sample NLL, argmax)
-static int forward_impl(dg_model *m) {
+int dg_forward_impl(dg_model *m) {
     dg_ctx *c = m->ctx;
     DG_REQUIRE(m->n > 0, "forward: no batch staged (call dg_model_set_batch_* first)");
     if (m->prec == DG_PREC_FP32) {
@@ -428,7 +480,7 @@ static int forward_impl(dg_model *m) {
     return 0;
 }
 
-static int backward_impl(dg_model *m) {
+int dg_backward_impl(dg_model *m) {
     dg_ctx *c = m->ctx;
     DG_REQUIRE(m->forward_done, "backward: call dg_forward first");
     DG_REQUIRE(m->have_targets, "backward: the staged batch has no targets");
@@ -451,7 +503,7 @@ static int backward_impl(dg_model *m) {
     return 0;
 }
 
-static int read_loss(dg_model *m, float *loss_out, int *errors_out) {
+int dg_read_loss(dg_model *m, float *loss_out, int *errors_out) {
     dg_ctx *c = m->ctx;
     if (!m->loss_reduced) if (int rc = dg_launch_loss_reduce(c, m->d_loss_n, m->d_argmax, m->d_targets, m->n, m->d_loss, m->d_errors)) return rc;
     if (loss_out) DG_CUDA(cudaMemcpyAsync(loss_out, m->d_loss, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -462,8 +514,9 @@ static int read_loss(dg_model *m, float *loss_out, int *errors_out) {
 
 extern "C" int dg_forward(dg_model *m, float *logprobs_out) {
     DG_REQUIRE(m, "dg_forward: model is NULL");
+    if (DG_MULTI(m)) return dgm_forward(m, logprobs_out);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
-    if (int rc = forward_impl(m)) return rc;
+    if (int rc = dg_forward_impl(m)) return rc;
     if (logprobs_out) {
         DG_CUDA(cudaMemcpyAsync(logprobs_out, m->d_logp, (size_t)m->n * DG_POINTS * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
         DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
@@ -473,15 +526,17 @@ extern "C" int dg_forward(dg_model *m, float *logprobs_out) {
 
 extern "C" int dg_loss_backward(dg_model *m, float *loss_out) {
     DG_REQUIRE(m, "dg_loss_backward: model is NULL");
+    if (DG_MULTI(m)) return dgm_loss_backward(m, loss_out);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (m->bf) if (int rc = dg_bf16_sync_grads(m)) return rc;      // this call accumulates into the gradient vector
-    if (int rc = backward_impl(m)) return rc;
-    if (loss_out) return read_loss(m, loss_out, nullptr);
+    if (int rc = dg_backward_impl(m)) return rc;
+    if (loss_out) return dg_read_loss(m, loss_out, nullptr);
     return 0;
 }
 
 extern "C" int dg_sgd_step(dg_model *m, float rate) {
     DG_REQUIRE(m, "dg_sgd_step: model is NULL");
+    if (DG_MULTI(m)) return dgm_sgd_step(m, rate);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (m->bf) { if (int rc = dg_bf16_sync_grads(m)) return rc; return dg_bf16_sgd_step(m, rate, nullptr); }
     return dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate);
@@ -493,8 +548,8 @@ static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
     // a deferring bf16 step keeps the whole gradient in the accumulation buffers (cleared inside the backward pass)
     if (!(m->bf && dg_bf16_defers_grads(m))) DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));      // train.lua:5
     m->fused_step = true;
-    int rc = forward_impl(m);                                              // train.lua:6
-    if (!rc) rc = backward_impl(m);                                        // train.lua:8-10
+    int rc = dg_forward_impl(m);                                              // train.lua:6
+    if (!rc) rc = dg_backward_impl(m);                                        // train.lua:8-10
     m->fused_step = false;
     if (rc) return rc;
     if (int rc2 = dg_dp_finish(c)) return rc2;                             // buckets were issued layer by layer in backward
@@ -504,6 +559,7 @@ static int train_step_body(dg_model *m, float rate, bool rate_from_device) {
 
 extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     DG_REQUIRE(m, "dg_train_step: model is NULL");
+    if (DG_MULTI(m)) return dgm_train_step(m, rate, loss_out);
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
     DG_REQUIRE(m->have_targets, "dg_train_step: the staged batch has no targets");
@@ -547,12 +603,13 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     } else {
         if (int rc = train_step_body(m, rate, false)) return rc;
     }
-    if (loss_out) return read_loss(m, loss_out, nullptr);
+    if (loss_out) return dg_read_loss(m, loss_out, nullptr);
     return 0;
 }
 
 extern "C" int dg_dp_allreduce_grads(dg_model *m) {
     DG_REQUIRE(m, "dg_dp_allreduce_grads: model is NULL");
+    if (DG_MULTI(m)) return 0;                 // dg_loss_backward on a multi-device model has summed the replicas' gradients already
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (m->bf) if (int rc = dg_bf16_sync_grads(m)) return rc;
     if (int rc = dg_dp_bucket(m->ctx, m->grads, m->P)) return rc;
@@ -561,6 +618,7 @@ extern "C" int dg_dp_allreduce_grads(dg_model *m) {
 
 extern "C" int dg_argmax(dg_model *m, int32_t *out) {
     DG_REQUIRE(m && out, "dg_argmax: NULL argument");
+    if (DG_MULTI(m)) return dgm_argmax(m, out);
     DG_REQUIRE(m->forward_done, "dg_argmax: call dg_forward first");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     DG_CUDA(cudaMemcpyAsync(out, m->d_argmax, (size_t)m->n * 4, cudaMemcpyDeviceToHost, m->ctx->stream));
@@ -570,8 +628,9 @@ extern "C" int dg_argmax(dg_model *m, int32_t *out) {
 
 extern "C" int dg_eval_batch(dg_model *m, int *errors_out, float *cost_out) {
     DG_REQUIRE(m, "dg_eval_batch: model is NULL");
+    if (DG_MULTI(m)) return dgm_eval_batch(m, errors_out, cost_out);
     DG_REQUIRE(m->have_targets, "dg_eval_batch: the staged batch has no targets");
     DG_CUDA(cudaSetDevice(m->ctx->dev));
-    if (int rc = forward_impl(m)) return rc;
-    return read_loss(m, cost_out, errors_out);
+    if (int rc = dg_forward_impl(m)) return rc;
+    return dg_read_loss(m, cost_out, errors_out);
 }

@@ -64,6 +64,8 @@ struct dg_ctx {
     // DG_TL=1: device buffer of globaltimer stamps {first CTA in, first CTA past the dependency wait, last CTA out} per kernel of the
     // step -- the only clock that sees inside a replayed CUDA graph (dg_prof_timeline)
     unsigned long long *tl = nullptr;
+    // dg_ctx_create_multi: this context stands for several devices of ONE process; kids[i] is the context of device i (multi.cu)
+    std::vector<dg_ctx *> kids;
 };
 enum { DG_TL_CONV0 = 0, DG_TL_CONV, DG_TL_HEAD, DG_TL_DGRAD, DG_TL_WGRAD, DG_TL_WGRAD0, DG_TL_FINALIZE, DG_TL_SGD, DG_TL_HEADRED, DG_TL_P2P, DG_TL_P2P_B, DG_TL_COUNT };
 
@@ -155,6 +157,8 @@ int dg_dp_finish(dg_ctx *ctx);
 #define DG_MAX_RANKS 8
 struct dg_p2p;
 int dg_dp_p2p_setup(dg_ctx *ctx, float *buf, size_t nfloats, dg_p2p **out);
+// the same mapping when all ranks are contexts of this process: peer access and plain pointers, no IPC, no NCCL
+int dg_dp_p2p_setup_local(dg_ctx *const *ctxs, float *const *bufs, size_t nfloats, int world, dg_p2p **out);
 int dg_dp_p2p_allreduce(dg_ctx *ctx, dg_p2p *p, cudaStream_t st, size_t off_floats, size_t n_floats, int chan, int scatter_only);
 int dg_dp_p2p_barrier(dg_ctx *ctx, dg_p2p *p, cudaStream_t st);
 void dg_dp_p2p_peers(const dg_p2p *p, const float **buf, int *world, size_t *per4);

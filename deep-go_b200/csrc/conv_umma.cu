@@ -2143,6 +2143,27 @@ int dg_bf16_dp_prepare(dg_model *m) {
     return 0;
 }
 
+// one process, several devices: the replicas of a multi-device model map each other's accumulation buffers directly
+int dg_bf16_dp_prepare_local(dg_model *const *kids, int n) {
+    std::vector<dg_ctx *> ctxs(n);
+    std::vector<float *> bufs(n);
+    std::vector<dg_p2p *> out(n, nullptr);
+    for (int k = 0; k < n; ++k) {
+        Bf16Path *b = kids[k]->bf;
+        DG_REQUIRE(b && b->defer_grads, "multi-device step: the bf16 path with gradient hand-off is required");
+        if (b->p2p) return 0;                                  // already mapped
+        ctxs[k] = kids[k]->ctx; bufs[k] = b->gacc;
+        DG_CUDA(cudaSetDevice(ctxs[k]->dev));
+        DG_CUDA(cudaStreamSynchronize(ctxs[k]->stream));
+    }
+    if (int rc = dg_dp_p2p_setup_local(ctxs.data(), bufs.data(), kids[0]->bf->gacc_floats, n, out.data())) {
+        for (dg_p2p *p : out) dg_dp_p2p_destroy(p);
+        return rc;
+    }
+    for (int k = 0; k < n; ++k) { kids[k]->bf->p2p = out[k]; kids[k]->bf->p2p_tried = true; kids[k]->bf->p2p_pull = false; }
+    return 0;
+}
+
 // materialise the conv layers' gradient of the last fused step in the Torch7-order vector (no-op when it already is there)
 int dg_bf16_sync_grads(dg_model *m) {
     Bf16Path *b = m->bf;

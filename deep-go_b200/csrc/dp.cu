@@ -49,6 +49,7 @@ extern "C" int dg_dp_unique_id(char id_out[128]) {
 
 extern "C" int dg_ctx_init_dp(dg_ctx *c, int rank, int world, const char id[128]) {
     DG_REQUIRE(c && id, "dg_ctx_init_dp: NULL argument");
+    DG_REQUIRE(c->kids.empty(), "dg_ctx_init_dp: a multi-device context is data parallel already (one process drives its devices)");
     DG_REQUIRE(world >= 1 && rank >= 0 && rank < world, "dg_ctx_init_dp: rank %d / world %d invalid", rank, world);
     c->rank = rank;
     c->world = world;
@@ -307,6 +308,38 @@ int dg_dp_p2p_setup(dg_ctx *c, float *buf, size_t nfloats, dg_p2p **out) {
     }
     p->args.rank = c->rank; p->args.world = c->world; p->args.off4 = 0; p->args.n4 = nfloats / 4; p->args.chan = 0; p->args.scatter_only = 0;
     *out = p;
+    return 0;
+}
+
+// Single process, one context per device (dg_ctx_create_multi): every context enables peer access to the others and uses their
+// buffers and flag blocks through plain device pointers.  out[r] receives rank r's mapping; all or nothing.
+int dg_dp_p2p_setup_local(dg_ctx *const *ctxs, float *const *bufs, size_t nfloats, int world, dg_p2p **out) {
+    DG_REQUIRE(world > 1 && world <= DG_MAX_RANKS, "peer exchange: needs 2..%d devices", DG_MAX_RANKS);
+    DG_REQUIRE(nfloats % 4 == 0, "peer exchange: buffer length must be a multiple of 4 floats");
+    for (int r = 0; r < world; ++r) out[r] = nullptr;
+    const size_t per4 = (nfloats / 4 + world - 1) / world;
+    for (int r = 0; r < world; ++r) {
+        DG_CUDA(cudaSetDevice(ctxs[r]->dev));
+        for (int q = 0; q < world; ++q) {
+            if (q == r) continue;
+            int can = 0;
+            DG_CUDA(cudaDeviceCanAccessPeer(&can, ctxs[r]->dev, ctxs[q]->dev));
+            DG_REQUIRE(can, "peer exchange: device %d cannot access device %d (numGPUs > 1 in one process needs peer access)", ctxs[r]->dev, ctxs[q]->dev);
+            cudaError_t pe = cudaDeviceEnablePeerAccess(ctxs[q]->dev, 0);
+            DG_REQUIRE(pe == cudaSuccess || pe == cudaErrorPeerAccessAlreadyEnabled, "cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", ctxs[r]->dev, ctxs[q]->dev, cudaGetErrorString(pe));
+            cudaGetLastError();
+        }
+        dg_p2p *p = new dg_p2p();
+        out[r] = p;
+        DG_CUDA(cudaMalloc((void **)&p->sig_local, 2 * sizeof(P2PSignals)));
+        DG_CUDA(cudaMemset(p->sig_local, 0, 2 * sizeof(P2PSignals)));
+        DG_CUDA(cudaMalloc((void **)&p->stage_local, per4 * world * 16));
+    }
+    for (int r = 0; r < world; ++r) {
+        dg_p2p *p = out[r];
+        for (int q = 0; q < world; ++q) { p->args.buf[q] = bufs[q]; p->args.sig[q] = out[q]->sig_local; p->args.stage[q] = out[q]->stage_local; }
+        p->args.rank = r; p->args.world = world; p->args.off4 = 0; p->args.n4 = nfloats / 4; p->args.chan = 0; p->args.scatter_only = 0;
+    }
     return 0;
 }
 

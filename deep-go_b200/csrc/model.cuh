@@ -39,7 +39,18 @@ struct dg_model {
     float *dz[2] = {nullptr, nullptr};
     // bf16 tcgen05 path
     Bf16Path *bf = nullptr;
+    // model on a multi-device context: one replica per device, the staged batch split on dim 0 (multi.cu)
+    std::vector<dg_model *> kids;
+    std::vector<int> kid_lo;           // first position of the staged batch on replica k
+    std::vector<float *> kid_gsum;     // per replica: the summed gradient vector of the separate-call path
 };
+
+// api.cu internals shared with multi.cu
+int dg_model_layout(dg_model *m, int num_layers, int channel_size, int in_planes, int k_first);
+int dg_forward_impl(dg_model *m);
+int dg_backward_impl(dg_model *m);
+int dg_read_loss(dg_model *m, float *loss_out, int *errors_out);
+int dg_bf16_dp_prepare_local(dg_model *const *kids, int n);   // conv_umma.cu
 
 // conv_umma.cu
 int dg_bf16_create(dg_model *m);

@@ -41,8 +41,11 @@ __global__ void fill_u8_kernel(uint8_t *p, int n, uint8_t v) {
     if (i < n) p[i] = v;
 }
 
+int dgm_predict_sym8(dg_model *m, float *probs_out, int32_t *argmax_out);      // multi.cu
+
 extern "C" int dg_predict_sym8(dg_model *m, float *probs_out, int32_t *argmax_out) {
     DG_REQUIRE(m, "dg_predict_sym8: model is NULL");
+    if (!m->kids.empty()) return dgm_predict_sym8(m, probs_out, argmax_out);
     DG_REQUIRE(m->have_raw && m->n > 0, "dg_predict_sym8: stage records with dg_model_set_batch_raw first");
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));

@@ -23,6 +23,7 @@ struct Node {
     int64_t offset = 0;
     std::vector<uint8_t> bytes;             // tensor: raw storage bytes
     int elem = 1;
+    bool is_double = false;
 };
 
 struct Parser {
@@ -38,7 +39,7 @@ struct Parser {
     std::string str() { int32_t n = i32(); std::string s; if (n >= 0 && need((size_t)n)) { s.assign((const char *)p, n); p += n; } else ok = false; return s; }
 
     int parse(int depth = 0) {
-        if (!ok || depth > 32) { ok = false; return -1; }
+        if (!ok || depth > 64) { ok = false; return -1; }
         const int tag = i32();
         Node n;
         switch (tag) {
@@ -81,28 +82,50 @@ struct Parser {
                 const int self = (int)nodes.size() - 1;
                 memo[ref] = self;
                 const int st = parse(depth + 1);
-                if (st >= 0 && nodes[st].kind == Node::TENSOR) { nodes[self].bytes = nodes[st].bytes; nodes[self].elem = nodes[st].elem; }
+                if (st >= 0 && nodes[st].kind == Node::TENSOR) { nodes[self].bytes = nodes[st].bytes; nodes[self].elem = nodes[st].elem; nodes[self].is_double = nodes[st].is_double; }
                 return self;
             }
             if (cls.size() > 7 && cls.compare(cls.size() - 7, 7, "Storage") == 0) {
                 int elem = 1;
                 if (cls == "torch.ByteStorage" || cls == "torch.CharStorage") elem = 1;
                 else if (cls == "torch.ShortStorage") elem = 2;
-                else if (cls == "torch.IntStorage" || cls == "torch.FloatStorage") elem = 4;
-                else if (cls == "torch.LongStorage" || cls == "torch.DoubleStorage") elem = 8;
+                else if (cls == "torch.IntStorage" || cls == "torch.FloatStorage" || cls == "torch.CudaStorage") elem = 4;   // cutorch writes floats
+                else if (cls == "torch.LongStorage" || cls == "torch.DoubleStorage" || cls == "torch.CudaDoubleStorage") elem = 8;
                 else { ok = false; return -1; }
                 const int64_t cnt = i64();
                 if (cnt < 0 || !need((size_t)cnt * elem)) { ok = false; return -1; }
                 n.kind = Node::TENSOR;
                 n.elem = elem;
+                n.is_double = cls.find("Double") != std::string::npos;
                 n.bytes.assign(p, p + cnt * elem);
                 p += cnt * elem;
                 nodes.push_back(n);
                 memo[ref] = (int)nodes.size() - 1;
                 return memo[ref];
             }
-            ok = false;
-            return -1;
+            // any other torch class (nn modules, criteria): the default serialisation writes the object's table next
+            {
+                nodes.push_back(n);
+                const int self = (int)nodes.size() - 1;
+                memo[ref] = self;
+                const int body = parse(depth + 1);
+                if (body >= 0 && nodes[body].kind == Node::TABLE) { nodes[self].kind = Node::TABLE; nodes[self].fields = nodes[body].fields; }
+                return self;
+            }
+        }
+        case 6: case 7: case 8: {
+            // a Lua function (Experiment:new copies the prototype's methods into every instance, so a pickled experiment carries
+            // them): reference index, string.dump bytes, then the table of upvalues.  Skipped.
+            const int ref = i32();
+            if (memo.count(ref)) return memo[ref];
+            const int32_t nbytes = i32();
+            if (nbytes < 0 || !need((size_t)nbytes)) { ok = false; return -1; }
+            p += nbytes;
+            nodes.push_back(n);
+            const int self = (int)nodes.size() - 1;
+            memo[ref] = self;
+            parse(depth + 1);
+            return self;
         }
         default: ok = false; return -1;
         }
@@ -152,5 +175,50 @@ extern "C" int dg_t7_read_record(const char *path, uint8_t *raw, int *x, int *y,
         dg_set_error("dg_t7_read_record: %s: move/ranks fields missing", path);
         return 5;
     }
+    return 0;
+}
+
+// experiment:load of a checkpoint the REFERENCE wrote (experiments.lua:124-131: torch.save of the pickled experiment table): the
+// flat parameter vector is the field modelParameters (model:getParameters(), experiments.lua:107; a Float, Cuda or Double tensor),
+// the rate lives in optimizer.rate (optimizer.lua:18-21).  Values missing from the file are left untouched.
+extern "C" int dg_t7_read_model(const char *path, float *params, size_t cap, size_t *n_out, double *rate, double *rate_decay,
+                                long long *iterations) {
+    if (!path || !n_out) { dg_set_error("dg_t7_read_model: NULL argument"); return 2; }
+    FILE *f = fopen(path, "rb");
+    if (!f) { dg_set_error("dg_t7_read_model: cannot open %s", path); return 4; }
+    std::vector<uint8_t> buf;
+    uint8_t tmp[1 << 16];
+    size_t got;
+    while ((got = fread(tmp, 1, sizeof tmp, f)) > 0) buf.insert(buf.end(), tmp, tmp + got);
+    fclose(f);
+    Parser ps;
+    ps.p = buf.data(); ps.end = buf.data() + buf.size();
+    const int root = ps.parse();
+    if (!ps.ok || root < 0 || ps.nodes[root].kind != Node::TABLE) { dg_set_error("dg_t7_read_model: %s is not a Torch7 table", path); return 5; }
+    auto &flds = ps.nodes[root].fields;
+    if (!flds.count("modelParameters") || ps.nodes[flds["modelParameters"]].kind != Node::TENSOR) {
+        dg_set_error("dg_t7_read_model: %s has no modelParameters tensor", path);
+        return 5;
+    }
+    const Node &t = ps.nodes[flds["modelParameters"]];
+    if (t.size.size() != 1 || (t.elem != 4 && t.elem != 8) || t.stride[0] != 1 || t.offset < 0 ||
+        (uint64_t)(t.offset + t.size[0]) * t.elem > t.bytes.size()) {
+        dg_set_error("dg_t7_read_model: %s: modelParameters is not a contiguous 1-D float tensor", path);
+        return 5;
+    }
+    *n_out = (size_t)t.size[0];
+    if (params) {
+        if (cap < *n_out) { dg_set_error("dg_t7_read_model: buffer holds %zu values, the file has %zu", cap, *n_out); return 2; }
+        for (size_t i = 0; i < *n_out; ++i) {
+            if (t.elem == 4 && !t.is_double) { float v; memcpy(&v, &t.bytes[(t.offset + i) * 4], 4); params[i] = v; }
+            else { double v; memcpy(&v, &t.bytes[(t.offset + i) * 8], 8); params[i] = (float)v; }
+        }
+    }
+    if (flds.count("optimizer") && ps.nodes[flds["optimizer"]].kind == Node::TABLE) {
+        auto &of = ps.nodes[flds["optimizer"]].fields;
+        if (rate && of.count("rate") && ps.nodes[of["rate"]].kind == Node::NUM) *rate = ps.nodes[of["rate"]].num;
+        if (rate_decay && of.count("rate_decay") && ps.nodes[of["rate_decay"]].kind == Node::NUM) *rate_decay = ps.nodes[of["rate_decay"]].num;
+    }
+    if (iterations && flds.count("iterations") && ps.nodes[flds["iterations"]].kind == Node::NUM) *iterations = (long long)ps.nodes[flds["iterations"]].num;
     return 0;
 }

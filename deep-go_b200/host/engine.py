@@ -37,9 +37,18 @@ def encode_labels(x, y, sym=None):
 
 class Context:
     def __init__(self, device=0):
+        """device: an int, or a list of ints for several GPUs inside this process (dg_ctx_create_multi: the reference's
+        numGPUs option, experiments.lua:10,155-168)."""
         self.L = _dg.lib()
         p = ffi.new("dg_ctx **")
-        check(self.L.dg_ctx_create(device, p))
+        if isinstance(device, (list, tuple)):
+            devs = ffi.new("int[]", [int(d) for d in device])
+            check(self.L.dg_ctx_create_multi(len(device), devs, p))
+            self.devices = list(device)
+            device = self.devices[0]
+        else:
+            check(self.L.dg_ctx_create(device, p))
+            self.devices = [device]
         self.h = ffi.gc(p[0], self.L.dg_ctx_destroy)
         self.device = device
 
@@ -210,9 +219,43 @@ class Model:
         check(self.L.dg_eval_batch(self.h, e, c))
         return int(e[0]), float(c[0])
 
+    def save_checkpoint(self, path, meta=None):
+        """dg_checkpoint_save: flat parameters + key=value header lines (meta: dict of scalars / strings)."""
+        text = "".join("%s=%s\n" % (k, v) for k, v in (meta or {}).items())
+        check(self.L.dg_checkpoint_save(self.h, str(path).encode(), text.encode()))
+
     def predict_sym8(self, want_probs=True):
         probs = np.empty((self.n, 361), np.float32) if want_probs else None
         am = np.empty(self.n, np.int32)
         check(self.L.dg_predict_sym8(self.h, ffi.cast("float *", probs.ctypes.data) if want_probs else ffi.NULL,
                                      ffi.cast("int32_t *", am.ctypes.data)))
         return probs, am
+
+
+def read_checkpoint(path):
+    """dg_checkpoint_read -> (meta dict of strings, float32 parameters)."""
+    L = _dg.lib()
+    n = ffi.new("size_t *")
+    meta = ffi.new("char[]", 1 << 16)
+    check(L.dg_checkpoint_read(str(path).encode(), meta, 1 << 16, ffi.NULL, 0, n))
+    params = np.empty(int(n[0]), np.float32)
+    check(L.dg_checkpoint_read(str(path).encode(), ffi.NULL, 0, ffi.cast("float *", params.ctypes.data), params.size, n))
+    d = {}
+    for line in ffi.string(meta).decode().splitlines():
+        if "=" in line:
+            k, v = line.split("=", 1)
+            d[k] = v
+    return d, params
+
+
+def read_reference_model(path):
+    """dg_t7_read_model: a checkpoint the reference wrote with torch.save -> (float32 parameters, rate, rate_decay, iterations);
+    scalars the file does not hold come back as None."""
+    L = _dg.lib()
+    n = ffi.new("size_t *")
+    rate, decay, it = ffi.new("double *", float("nan")), ffi.new("double *", float("nan")), ffi.new("long long *", -1)
+    check(L.dg_t7_read_model(str(path).encode(), ffi.NULL, 0, n, ffi.NULL, ffi.NULL, ffi.NULL))
+    params = np.empty(int(n[0]), np.float32)
+    check(L.dg_t7_read_model(str(path).encode(), ffi.cast("float *", params.ctypes.data), params.size, n, rate, decay, it))
+    nn = lambda v: None if v != v else v
+    return params, nn(rate[0]), nn(decay[0]), (None if it[0] < 0 else int(it[0]))

@@ -4,7 +4,6 @@ channelSize, rate, rateDecay, criterion), getBasicModel and makeDataParallel.  T
 dg_model: forward/backward/getParameters keep the nn.Module call shape used by train.lua."""
 import copy
 import os
-import pickle
 import random
 import time
 
@@ -18,6 +17,8 @@ from .train import train
 class ClassNLLCriterion:
     """nn.ClassNLLCriterion() (experiments.lua:45): sizeAverage mean NLL; forward/backward are fused into the
     device step, these methods only expose the numbers in the reference's call order (train.lua:8-9,37)."""
+
+    fused = True        # mean NLL with sizeAverage is what dg_train_step computes: train() may fuse eval() with the update
 
     def cuda(self):
         return self
@@ -63,6 +64,7 @@ class PolicyNet:
     def __init__(self, numLayers, kernels, channels, precision=engine.DG_PREC_BF16, max_batch=2048, device=0):
         assert len(kernels) == numLayers and len(channels) == numLayers + 1
         assert all(k == 3 for k in kernels[1:]) and all(c == channels[1] for c in channels[1:-1]) and channels[-1] == 1
+        self.spec = dict(numLayers=numLayers, kernels=list(kernels), channels=list(channels), precision=precision, max_batch=max_batch)
         self.ctx = engine.Context(device)
         self.engine = engine.Model(self.ctx, numLayers, channels[1], precision, max_batch, channels[0], kernels[0])
         self._targets = None
@@ -93,16 +95,33 @@ class PolicyNet:
     def backward(self, inputs, dfdo):
         return self.engine.loss_backward()
 
+    def train_step(self, inputs, targets1, rate):
+        """eval() + optimizer:step of train.lua:111,131 as ONE device call (dg_train_step: the captured step graph, and with
+        several GPUs the in-graph gradient exchange); returns the cost eval() would have returned."""
+        self.stage(inputs, targets1)
+        return self.engine.train_step(rate)
+
+
+default_device = 0        # cutorch.setDevice (default-experiment.lua:6, experiments/repeated.lua:12), 0-based here
+
 
 def getBasicModel(numLayers, kernels, channels, **kw):
+    kw.setdefault("device", default_device)
     return PolicyNet(numLayers, kernels, channels, **kw)
 
 
 def makeDataParallel(model, nGPU):
-    """experiments.lua:155-168.  Here data parallelism is one process per GPU (host/dp.py); inside one process the
-    model is returned unchanged, as the reference does for nGPU == 1."""
+    """experiments.lua:155-168: for nGPU > 1 the model becomes nGPU replicas, one per device of THIS process, behind the same
+    interface (nn.DataParallelTable(1): batches split on the batch dimension, gradients summed); the parameters are carried
+    over.  nGPU == 1 returns the model unchanged, as the reference does.  (One process per GPU is the other way to the same
+    result: host/dp.py.)"""
     if nGPU > 1:
         assert nGPU <= engine.device_count(), "number of GPUs less than nGPU specified"
+        params = model.engine.get_params()
+        spec = model.spec
+        model = PolicyNet(spec["numLayers"], spec["kernels"], spec["channels"], precision=spec["precision"],
+                          max_batch=spec["max_batch"], device=list(range(nGPU)))
+        model.engine.set_params(params)
     return model
 
 
@@ -158,30 +177,76 @@ class Experiment:
         return train_costs, validation_costs
 
     def pickle(self):
+        """experiments.lua:55-61: everything but the data sets; the model goes as its flat parameter vector"""
         skip = {"datasets", "model", "modelParameters", "grads", "criterion"}
         d = {k: v for k, v in self.__dict__.items() if k not in skip}
         d["parameters"] = self.modelParameters.numpy()
         return d
 
+    _SCALARS = ("name", "useCuda", "numGPUs", "data_root", "validationSize", "validation_interval", "batchSize", "rate", "rateDecay",
+                "id", "iterations", "precision")
+
     def save(self, opt_filename=None):
-        """experiment:save() (experiments.lua:124-127): flat parameters + optimizer rate + iterations + costs"""
+        """experiment:save() (experiments.lua:124-127).  One checkpoint format for every host of the library
+        (dg_checkpoint_save): the flat parameters plus what a resumed run needs -- options, optimizer rate, iterations, costs."""
         filename = opt_filename or "%s.model" % self.id
-        with open(filename, "wb") as f:
-            pickle.dump(self.pickle(), f)
+        meta = {k: getattr(self, k) for k in self._SCALARS if hasattr(self, k)}
+        meta["kernels0"], meta["channels0"] = self.kernels[0], self.channels[0]
+        meta["optimizer_rate"] = repr(self.optimizer.rate)
+        meta["optimizer_rate_decay"] = repr(self.optimizer.rate_decay)
+        meta["validation_costs"] = ",".join(repr(float(v)) for v in self.validation_costs)
+        meta["directories"] = ",".join("%s:%s" % kv for kv in sorted(self.directories.items()))
+        self.model.engine.save_checkpoint(filename, meta)
         return filename
 
     @staticmethod
-    def load(filename):
+    def load(filename, **overrides):
+        """Experiment:load (experiments.lua:129-131 + unpickle :63-72): rebuild the experiment and its model from a checkpoint of
+        this library, or -- for a file the reference wrote with torch.save -- take the flat parameter vector, rate and
+        iteration count from it and the options from basicGoExperiment."""
         with open(filename, "rb") as f:
-            d = pickle.load(f)
-        params = d.pop("parameters")
-        e = Experiment(**d)
-        e.initialized = False
-        keep = (e.iterations, e.validation_costs, e.optimizer, e.id)
-        e.kernels, e.strides, e.channels = [e.kernels[0]], [1], [e.channels[0]]
+            native = f.read(9) == b"DGCKPT02\n"
+        if not native:
+            return Experiment.load_reference(filename, **overrides)
+        meta, params = engine.read_checkpoint(filename)
+        conv = {"useCuda": lambda v: v == "True", "numGPUs": int, "validationSize": int, "validation_interval": int, "batchSize": int,
+                "rate": float, "rateDecay": float, "id": lambda v: v, "iterations": int, "precision": int, "name": str, "data_root": str}
+        kw = {k: conv[k](meta[k]) for k in conv if k in meta}
+        for k in ("id",):
+            try:
+                kw[k] = float(kw[k])
+            except (KeyError, ValueError):
+                pass
+        if meta.get("directories"):
+            kw["directories"] = dict(kv.split(":", 1) for kv in meta["directories"].split(","))
+        kw.update(overrides)                      # e.g. data_root on another machine
+        iterations = kw.pop("iterations", 0)
+        ident = kw.pop("id", None)
+        e = Experiment(criterion=ClassNLLCriterion(), kernels=[int(meta.get("kernels0", meta["kFirst"]))], strides=[1],
+                       channels=[int(meta.get("channels0", meta["inPlanes"]))], numLayers=int(meta["numLayers"]),
+                       channelSize=int(meta["channelSize"]), **kw)
         e.init()
-        e.iterations, e.validation_costs, e.optimizer, e.id = keep
+        e.iterations = iterations
+        if ident is not None:
+            e.id = ident
+        e.validation_costs = [float(v) for v in meta.get("validation_costs", "").split(",") if v]
+        e.optimizer = SGD.new(float(meta.get("optimizer_rate", e.rate)), float(meta.get("optimizer_rate_decay", e.rateDecay)))
         e.modelParameters.copy(params)
+        return e
+
+    @staticmethod
+    def load_reference(filename, proto=None, **kw):
+        """A `.model` file of the reference itself: the architecture follows from the length of its flat vector
+        (numLayers x channelSize of `proto`, default basicGoExperiment, must match)."""
+        params, rate, decay, iterations = engine.read_reference_model(filename)
+        e = (proto or basicGoExperiment).new(kw)
+        e.init()
+        assert e.model.engine.P == len(params), "the checkpoint holds %d parameters, the experiment's model has %d" % (len(params), e.model.engine.P)
+        e.modelParameters.copy(params)
+        if rate is not None:
+            e.optimizer = SGD.new(rate, decay if decay is not None else e.rateDecay)
+        if iterations is not None:
+            e.iterations = iterations
         return e
 
 

@@ -18,3 +18,7 @@ class SGD:
         assert parameters.model is grad.model
         parameters.model.engine.sgd_step(self.rate)
         self.rate = self.rate * (1 - self.rate_decay)
+
+    def after_fused_step(self):
+        """The update itself ran inside dg_train_step with self.rate; what is left of SGD:step is the decay (optimizer.lua:26)."""
+        self.rate = self.rate * (1 - self.rate_decay)

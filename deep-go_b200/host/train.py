@@ -1,6 +1,6 @@
 """Host mirror of train.lua: eval (:4-12), eval_validation (:14-45) and train (:47-142) with the reference's
 bookkeeping (EMA cost .95/.05, print every 10 iterations, validation + save every validation_interval).
-The reference's duplicate eval inside pcall (train.lua:106) is reduced to one guarded eval."""
+The reference's duplicate eval inside pcall (train.lua:106) is reduced to one eval."""
 import time
 
 import numpy as np
@@ -52,9 +52,19 @@ def train(experiment, params):
     _data.do_queued_tasks()
     total_start = time.time()
 
+    # eval() + optimizer:step are ONE device call (dg_train_step: captured step graph, in-graph gradient exchange on several GPUs)
+    # whenever nothing has to happen between them.  The reference validates and saves BETWEEN eval and the update
+    # (train.lua:111-131): those iterations keep the two separate calls, so every printed number is what the reference prints.
+    fused_ok = hasattr(model, "train_step") and hasattr(optimizer, "after_fused_step") and hasattr(criterion, "fused") \
+        and not params.get("separate_calls", False)
+
     def train_iter(train_set):
         t0 = time.time()
-        train_cost, _ = eval(model, grads, train_set["input"], train_set["output"], criterion)
+        fused = fused_ok and (experiment.iterations + 1) % experiment.validation_interval != 0
+        if fused:
+            train_cost = model.train_step(train_set["input"], train_set["output"], optimizer.rate)
+        else:
+            train_cost, _ = eval(model, grads, train_set["input"], train_set["output"], criterion)
         iter_time = time.time() - t0
         if state["cost_average"] is None:
             state["cost_average"] = train_cost
@@ -70,7 +80,10 @@ def train(experiment, params):
             else:
                 print("training", state["cost_average"], "(samples per second %s)" % (batchSize / iter_time))
             train_costs.append(state["cost_average"])
-        optimizer.step(parameters, grads)
+        if fused:
+            optimizer.after_fused_step()
+        else:
+            optimizer.step(parameters, grads)
 
     for _ in range(iters):
         _data.queue_on_minibatch(train_iter, datasets["train"], batchSize, base)

@@ -41,6 +41,15 @@ function M.context(device)
     return ffi.gc(p[0], M.lib.dg_ctx_destroy)
 end
 
+-- numGPUs > 1 inside this process (experiments.lua:155-168): one context standing for devices 0 .. n-1
+function M.context_multi(n)
+    local devs = ffi.new('int[?]', n)
+    for i = 0, n - 1 do devs[i] = i end
+    local p = ffi.new('dg_ctx *[1]')
+    M.check(M.lib.dg_ctx_create_multi(n, devs, p))
+    return ffi.gc(p[0], M.lib.dg_ctx_destroy)
+end
+
 function M.model(ctx, numLayers, channelSize, kFirst, precision, maxBatch)
     local p = ffi.new('dg_model *[1]')
     M.check(M.lib.dg_model_create(ctx, numLayers, channelSize, 37, kFirst or 5, precision or M.PREC_BF16, maxBatch, p))

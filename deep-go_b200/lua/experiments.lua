@@ -47,6 +47,14 @@ end
 function Model:backward(mb, df_do)
     dg.check(lib.dg_loss_backward(self.handle, nil))
 end
+-- eval() + optimizer:step (train.lua:111,131) as ONE device call: the captured step graph, with the gradient exchange inside it when
+-- the model spans several GPUs; returns the cost eval() would have returned
+function Model:train_step(mb, rate)
+    stage(self, mb)
+    local loss = ffi.new('float[1]')
+    dg.check(lib.dg_train_step(self.handle, rate, loss))
+    return loss[0]
+end
 function Model:eval_slice(mb, targets, lo, hi)
     local n = hi - lo + 1
     local off = lo - 1
@@ -72,7 +80,8 @@ end
 function getBasicModel(numLayers, kernels, channels, opt)
     opt = opt or {}
     local self = setmetatable({}, Model)
-    self.ctx = dg.context(opt.device or 0)
+    self.opt = {numLayers = numLayers, channelSize = channels[2], kFirst = kernels[1], precision = opt.precision, maxBatch = opt.maxBatch or 2048}
+    self.ctx = dg.context(opt.device or default_device or 0)
     self.handle = dg.model(self.ctx, numLayers, channels[2], kernels[1], opt.precision, opt.maxBatch or 2048)
     local n = ffi.new('size_t[1]')
     dg.check(lib.dg_model_param_count(self.handle, n))
@@ -80,13 +89,24 @@ function getBasicModel(numLayers, kernels, channels, opt)
     return self
 end
 
--- one process per GPU: the launcher starts numGPUs processes (torchrun-style env RANK / WORLD_SIZE) and every rank
--- binds the library's NCCL communicator; inside one process the model is returned unchanged (experiments.lua:155-168)
+-- experiments.lua:155-168: for nGPU > 1 the model becomes nGPU replicas, one per device of this process, behind the same handle
+-- (nn.DataParallelTable(1): batches split on the batch dimension, gradients summed over NVLink peer memory inside the library);
+-- the parameters are carried over.  nGPU == 1 returns the model unchanged, as the reference does.
 function makeDataParallel(model, nGPU)
     if nGPU > 1 then
         local count = ffi.new('int[1]')
         dg.check(lib.dg_device_count(count))
         assert(nGPU <= count[0], 'number of GPUs less than nGPU specified')
+        local buf = ffi.new('float[?]', model.P)
+        dg.check(lib.dg_model_get_params(model.handle, buf, model.P))
+        local o = model.opt
+        local multi = setmetatable({}, getmetatable(model))
+        multi.opt = o
+        multi.ctx = dg.context_multi(nGPU)
+        multi.handle = dg.model(multi.ctx, o.numLayers, o.channelSize, o.kFirst, o.precision, o.maxBatch)
+        multi.P = model.P
+        dg.check(lib.dg_model_set_params(multi.handle, buf, multi.P))
+        model = multi
     end
     return model
 end
@@ -148,28 +168,57 @@ function Experiment:run(params)
     return train_cost, validation_cost
 end
 
--- checkpoint = flat parameter vector (Torch7 order) + optimizer rate + iteration count (experiments.lua:124-131)
+-- experiment:save / Experiment:load (experiments.lua:124-131).  One checkpoint format for every host of the library
+-- (dg_checkpoint_save / dg_checkpoint_read: "DGCKPT02", key=value lines, "end", P float32 in Torch7 getParameters order); a file the
+-- reference wrote with torch.save is read with dg_t7_read_model.
 function Experiment:save(opt_filename)
     local filename = opt_filename or (self.id .. '.model')
-    local buf = ffi.new('float[?]', self.model.P)
-    self.modelParameters:get(buf)
-    local f = assert(io.open(filename, 'wb'))
-    f:write(string.format("deepgo-b200 %d %d %d %.17g %d\n", self.numLayers, self.channelSize, self.model.P, self.optimizer.rate, self.iterations))
-    f:write(ffi.string(buf, self.model.P * 4))
-    f:close()
+    local costs = {}
+    for i, v in ipairs(self.validation_costs) do costs[i] = string.format("%.17g", v) end
+    local meta = string.format("name=%s\nrate=%.17g\nrateDecay=%.17g\nbatchSize=%d\nvalidationSize=%d\nvalidation_interval=%d\nnumGPUs=%d\n" ..
+                               "id=%s\niterations=%d\noptimizer_rate=%.17g\noptimizer_rate_decay=%.17g\nvalidation_costs=%s\ndata_root=%s\n",
+                               self.name or "", self.rate, self.rateDecay, self.batchSize, self.validationSize, self.validation_interval, self.numGPUs,
+                               tostring(self.id), self.iterations, self.optimizer.rate, self.optimizer.rate_decay, table.concat(costs, ","), self.data_root)
+    dg.check(lib.dg_checkpoint_save(self.model.handle, filename, meta))
 end
 
 function Experiment:load(filename)
     local f = assert(io.open(filename, 'rb'))
-    local L, C, P, rate, iterations = f:read('*l'):match("deepgo%-b200 (%d+) (%d+) (%d+) (%S+) (%d+)")
-    local e = self:new{numLayers = tonumber(L), channelSize = tonumber(C)}
-    e:init()
-    local bytes = f:read(tonumber(P) * 4)
+    local native = f:read(9) == "DGCKPT02\n"
     f:close()
-    local buf = ffi.new('float[?]', tonumber(P))
-    ffi.copy(buf, bytes, tonumber(P) * 4)
+    local n = ffi.new('size_t[1]')
+    if not native then
+        -- the reference's own checkpoint: flat vector, rate and iteration count; options from this prototype
+        local rate, decay, iters = ffi.new('double[1]', -1), ffi.new('double[1]', -1), ffi.new('long long[1]', -1)
+        dg.check(lib.dg_t7_read_model(filename, nil, 0, n, nil, nil, nil))
+        local e = self:new()
+        e:init()
+        assert(tonumber(n[0]) == e.model.P, "the checkpoint's parameter count does not match the experiment's model")
+        local buf = ffi.new('float[?]', e.model.P)
+        dg.check(lib.dg_t7_read_model(filename, buf, e.model.P, n, rate, decay, iters))
+        e.modelParameters:set(buf)
+        if rate[0] >= 0 then e.optimizer = SGD.new(rate[0], decay[0] >= 0 and decay[0] or e.rateDecay) end
+        if iters[0] >= 0 then e.iterations = tonumber(iters[0]) end
+        return e
+    end
+    local meta = ffi.new('char[65536]')
+    dg.check(lib.dg_checkpoint_read(filename, meta, 65536, nil, 0, n))
+    local kv = {}
+    for k, v in ffi.string(meta):gmatch("([%w_]+)=([^\n]*)\n") do kv[k] = v end
+    local e = self:new{numLayers = tonumber(kv.numLayers), channelSize = tonumber(kv.channelSize), kernels = {tonumber(kv.kFirst)},
+                       strides = {1}, channels = {tonumber(kv.inPlanes)}, rate = tonumber(kv.rate) or self.rate,
+                       rateDecay = tonumber(kv.rateDecay) or self.rateDecay, batchSize = tonumber(kv.batchSize) or self.batchSize,
+                       validationSize = tonumber(kv.validationSize) or self.validationSize,
+                       validation_interval = tonumber(kv.validation_interval) or self.validation_interval,
+                       numGPUs = tonumber(kv.numGPUs) or 1, name = kv.name, data_root = kv.data_root or self.data_root}
+    e:init()
+    local buf = ffi.new('float[?]', e.model.P)
+    dg.check(lib.dg_checkpoint_read(filename, nil, 0, buf, e.model.P, n))
     e.modelParameters:set(buf)
-    e.optimizer = SGD.new(tonumber(rate), e.rateDecay)
-    e.iterations = tonumber(iterations)
+    e.optimizer = SGD.new(tonumber(kv.optimizer_rate) or e.rate, tonumber(kv.optimizer_rate_decay) or e.rateDecay)
+    e.iterations = tonumber(kv.iterations) or 0
+    e.id = tonumber(kv.id) or kv.id
+    e.validation_costs = {}
+    for v in (kv.validation_costs or ""):gmatch("[^,]+") do table.insert(e.validation_costs, tonumber(v)) end
     return e
 end

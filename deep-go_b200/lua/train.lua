@@ -43,7 +43,11 @@ function train(experiment, params)
 
     local function train_iter(train_set)
         local iter_start_time = os.clock()
+        -- eval() and the update are ONE device call unless the reference does something between them (validation + save,
+        -- train.lua:119-124): those iterations keep the separate calls, so every printed number is the reference's
+        local fused = model.train_step ~= nil and (experiment.iterations + 1) % experiment.validation_interval ~= 0
         local ok, train_cost = pcall(function()
+            if fused then return model:train_step(train_set, optimizer.rate) end
             local c = eval(model, grads, train_set, train_set.output, criterion)
             return c
         end)
@@ -63,7 +67,8 @@ function train(experiment, params)
             end
             table.insert(train_costs, cost_average)
         end
-        optimizer:step(parameters, grads)
+        if fused then optimizer.rate = optimizer.rate * (1 - optimizer.rate_decay)      -- the decay of SGD:step (optimizer.lua:26)
+        else optimizer:step(parameters, grads) end
     end
 
     for i = 1, iters do queue_on_minibatch(train_iter, datasets.train, batchSize) end

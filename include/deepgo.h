@@ -43,6 +43,15 @@ int dg_device_count(int *out);
 
 /* ---- context: one device, one stream (cutorch.setDevice, default-experiment.lua:6) --------- */
 int dg_ctx_create(int device, dg_ctx **out);
+/* numGPUs > 1 inside ONE process (experiments.lua:10,97-103,155-168: makeDataParallel wraps the model in
+ * nn.DataParallelTable(1)): a context that stands for ndev devices.  A model created on it is one replica per device;
+ * dg_model_set_batch_* split the batch on dim 0 into near-equal contiguous chunks as DataParallelTable does (n >= ndev),
+ * every replica scales its loss gradient by 1/n, and dg_train_step / dg_loss_backward sum the replicas' gradients over
+ * NVLink peer memory (cudaDeviceEnablePeerAccess; no NCCL, no second process) before the update, so the replicas stay
+ * bit-identical.  Results (log-probs, argmax, loss, errors) come back for the whole batch; parameters and gradients are
+ * read from replica 0.  One caller thread drives all devices.  ndev == 1 is dg_ctx_create.  The stand-alone entry points
+ * (dg_encode, dg_summarize_boards, dg_update_boards, timers, profiling) use the first device. */
+int dg_ctx_create_multi(int ndev, const int *devs, dg_ctx **out);
 int dg_ctx_destroy(dg_ctx *ctx);
 int dg_ctx_synchronize(dg_ctx *ctx);
 /* kernels this library has launched on ctx so far (bench.py "gpu_launches") */
@@ -110,6 +119,18 @@ int dg_encode_labels(const uint8_t *x, const uint8_t *y, const uint8_t *sym, int
 /* torch.load of one position record (dataloader.lua:123-125) without Torch7: fills raw u8[9*19*19] and the
  * 1-based move / player / ranks exactly as stored.  Host-only, reentrant (loader threads, data.lua:14-19). */
 int dg_t7_read_record(const char *path, uint8_t *raw, int *x, int *y, int *player, int ranks[2]);
+
+/* ---- checkpoints (experiment:save / Experiment:load, experiments.lua:55-72,124-131) -------------------------------- */
+/* One format for every host of this library: "DGCKPT02" + key=value lines (numLayers, channelSize, kFirst, inPlanes, P written here,
+ * then the caller's own lines `meta`: rate, rateDecay, iterations, ..) + "end" + P float32 parameters in Torch7 getParameters
+ * order.  dg_checkpoint_read returns the header lines in meta (may be NULL), the count in *n_out and, when params is not NULL, the
+ * parameters.  Host only apart from the parameter read-back. */
+int dg_checkpoint_save(dg_model *m, const char *path, const char *meta);
+int dg_checkpoint_read(const char *path, char *meta, size_t meta_cap, float *params, size_t cap, size_t *n_out);
+/* A checkpoint written by the REFERENCE (torch.save of the pickled experiment, experiments.lua:124-127): extracts the flat
+ * parameter vector (field modelParameters, experiments.lua:107; Float, Cuda or Double tensor) and, where present, optimizer.rate,
+ * optimizer.rate_decay (optimizer.lua:18-21) and iterations.  params may be NULL to query the count.  Host only, reentrant. */
+int dg_t7_read_model(const char *path, float *params, size_t cap, size_t *n_out, double *rate, double *rate_decay, long long *iterations);
 
 /* ---- packed corpus + native minibatch loader -------------------------------- */
 /* The reference keeps one Torch7 file per position and loads a minibatch with n torch.load calls in a pool of Lua threads

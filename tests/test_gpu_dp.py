@@ -71,3 +71,80 @@ def test_ranks_match_one_gpu(tmp_path, prec, world):
         assert np.array_equal(ga, np.load(str(tmp_path / "out") + ".g%d.npy" % r)), r     # the summed gradient of the last step, materialised on demand
     tol = 1e-5 if prec == 0 else 2e-3
     assert np.abs(a - ref).max() < tol
+
+
+# ---- several GPUs inside ONE process: the reference's numGPUs option (experiments.lua:10,155-168) -------------------------------
+def _golden_batch(n, step=7):
+    g = np.load(os.path.join(entry.ROOT, "tests", "golden", "positions.npz"))
+    idx = np.arange(0, n * step, step); pl = g["player"][idx]
+    return dict(raw=g["raw"][idx], player=pl, rank=g["ranks"][idx, pl - 1], x=g["x"][idx], y=g["y"][idx])
+
+
+@pytest.mark.parametrize("prec,world", [(0, 2), (1, 2), (1, 8)])
+def test_multi_device_context_matches_one_gpu(prec, world):
+    """dg_ctx_create_multi: one model handle over `world` devices trains like one GPU on the whole batch -- same log-probs, same
+    loss, same top-1 errors, parameters within the summation-order tolerance; uneven split (n % world != 0) included."""
+    entry.build()
+    from deepgo_b200.host import engine
+    if engine.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    n = 2 * world + 3
+    b = _golden_batch(n)
+    one = engine.Model(engine.Context(0), 4, 64, prec, max_batch=n)
+    multi = engine.Model(engine.Context(list(range(world))), 4, 64, prec, max_batch=n)
+    rng = np.random.default_rng(1)
+    flat = rng.normal(0, 0.05, one.P).astype(np.float32)
+    tol = 1e-5 if prec == 0 else 2e-3
+    for m in (one, multi):
+        m.set_params(flat)
+        m.set_batch_raw(b["raw"], b["player"], b["rank"], None, b["x"], b["y"])
+    lp1, lpm = one.forward(), multi.forward()
+    assert np.array_equal(lp1, lpm)                              # the forward pass of a position does not depend on its batch
+    assert np.array_equal(one.argmax(), multi.argmax())
+    e1, c1 = one.eval_batch(); em, cm = multi.eval_batch()
+    assert e1 == em and abs(c1 - cm) < 1e-5
+    # separate calls (eval() then SGD:step): the gradient vector is the whole-batch mean on both
+    for m in (one, multi):
+        m.forward(False); m.zero_grads(); m.loss_backward()
+    g1, gm = one.get_grads(), multi.get_grads()
+    assert np.abs(g1).max() > 0 and np.abs(g1 - gm).max() < tol * max(1.0, np.abs(g1).max())
+    # fused steps
+    for _ in range(3):
+        l1 = lm = None
+        for m in (one, multi):
+            m.set_batch_raw(b["raw"], b["player"], b["rank"], None, b["x"], b["y"])
+        l1, lm = one.train_step(0.05), multi.train_step(0.05)
+        assert abs(l1 - lm) < tol
+    assert np.abs(one.get_params() - multi.get_params()).max() < tol
+    with pytest.raises(Exception):                               # fewer positions than devices
+        multi.set_batch_raw(b["raw"][:world - 1], b["player"][:world - 1], b["rank"][:world - 1])
+
+
+def test_experiment_numgpus_2(tmp_path, capsys):
+    """Experiment{useCuda = true, numGPUs = 2}:run{iters} (experiments.lua:97-103) equals the one-GPU run on the same minibatches."""
+    entry.build()
+    from deepgo_b200.host import engine, experiments
+    if engine.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import random
+    import shutil
+    rec = os.path.join(entry.ROOT, "tests", "golden", "records")
+    root = tmp_path / "root"
+    shutil.copytree(os.path.join(rec, "data"), root / "data")
+    for split in ("train", "validation"):
+        shutil.copyfile(root / "data" / "test_game_counts.txt", root / "data" / (split + "_game_counts.txt"))
+    os.chdir(tmp_path)
+    runs = []
+    for ngpu in (1, 2):
+        e = experiments.basicGoExperiment.new(dict(useCuda=True, numGPUs=ngpu, data_root=str(root / "data"), validation_interval=20,
+                                                   validationSize=8, batchSize=6, precision=1, rate=0.05))
+        e.init()
+        assert len(e.model.ctx.devices) == ngpu
+        rng = np.random.default_rng(9)
+        e.modelParameters.copy(rng.normal(0, 0.05, e.model.engine.P).astype(np.float32))
+        random.seed(4)
+        costs, vcosts = e.run({"iters": 20, "base": str(root)})
+        runs.append((costs, vcosts, e.modelParameters.numpy()))
+    (c1, v1, p1), (c2, v2, p2) = runs
+    assert np.allclose(c1, c2, atol=2e-3) and np.allclose(v1, v2, atol=2e-3)
+    assert np.abs(p1 - p2).max() < 2e-3

@@ -135,3 +135,113 @@ def test_localtest_replay(host, tmp_path, capsys, precision):
     fn = e.save(str(tmp_path / "ck.model"))
     e2 = ex.Experiment.load(fn)
     assert e2.iterations == 20 and np.array_equal(e2.modelParameters.numpy(), e.modelParameters.numpy())
+
+
+def _experiment(host, root, tmp_path, **kw):
+    ex = host["experiments"]
+    opts = dict(useCuda=False, data_root=str(root / "data"), validation_interval=20, validationSize=10, batchSize=4, precision=0, rate=0.05)
+    opts.update(kw)
+    e = ex.basicGoExperiment.new(opts)
+    os.chdir(tmp_path)
+    e.init()
+    rng = np.random.default_rng(5)
+    flat = rng.normal(0, 0.05, e.model.engine.P).astype(np.float32)
+    e.modelParameters.copy(flat)
+    return e, flat
+
+
+def _oracle_batch_of(host, names, root):
+    from oracle import encode
+    recs = [host["dataloader"].read_record(os.path.join(str(root), n)) for n in names]
+    raw = np.stack([r["input"] for r in recs])
+    pl = np.array([r["move"]["player"] for r in recs]); rk = np.array([r["ranks"][p] for r, p in zip(recs, pl)])
+    xs = np.array([r["move"]["x"] for r in recs]); ys = np.array([r["move"]["y"] for r in recs])
+    return encode.load_minibatch(raw, pl, rk, xs, ys)
+
+
+@pytest.mark.gpu
+def test_eval_validation_equals_oracle(host, tmp_path):
+    """train.lua:14-45 on the device against oracle.net.eval_validation, aggregate quirks included: V = 10, batch 4 -> two batches
+    (the tail of 2 is dropped, :24), weights batchSize - 1 (:39), divisor V (:44)."""
+    import torch
+    from oracle import net
+    root = _make_tree(tmp_path)
+    e, flat = _experiment(host, root, tmp_path)
+    import random
+    random.seed(11)
+    ds = e.datasets["validation"]
+    names = [ds.generate_random_filename() for _ in range(10)]
+    x, t = _oracle_batch_of(host, names, root)
+    cost, acc = host["train"].eval_validation(e, x.astype(np.float32), (t + 1).astype(np.float64))
+    cost_o, acc_o = net.eval_validation(torch.from_numpy(flat).double(), torch.from_numpy(x), t, 4, e.numLayers, e.channelSize)
+    assert abs(cost - cost_o) < 1e-4 and acc == acc_o
+    assert abs(cost_o - (3 * 2 * 5.88) / 10) < 0.5          # the quirk is really in: 2 batches x weight 3 over V = 10, costs near ln 361
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("separate", [False, True])
+def test_train_bookkeeping_equals_oracle_replay(host, tmp_path, capsys, separate):
+    """30 iterations of train() (train.lua:47-142) against a pure-oracle replay of the same minibatches: the EMA cost list (one entry
+    per 10 iterations, .95/.05, seeded with the first cost), the validation at iteration 20 BEFORE that iteration's update, the
+    decayed rate.  Both ways through the library: eval() and the update fused into dg_train_step, and as separate calls."""
+    import random
+    import torch
+    from oracle import net
+    root = _make_tree(tmp_path)
+    e, flat = _experiment(host, root, tmp_path)
+    iters, B, V = 30, e.batchSize, e.validationSize
+    random.seed(21)
+    costs, vcosts = e.run({"iters": iters, "base": str(root), "separate_calls": separate})
+    out = capsys.readouterr().out
+    # ---- replay
+    random.seed(21)
+    vnames = [e.datasets["validation"].generate_random_filename() for _ in range(V)]
+    tnames = [[e.datasets["train"].generate_random_filename() for _ in range(B)] for _ in range(iters)]
+    vx, vt = _oracle_batch_of(host, vnames, root)
+    p = torch.from_numpy(flat).double()
+    rate, avg, want, vwant = 0.05, None, [], []
+    for it in range(1, iters + 1):
+        x, t = _oracle_batch_of(host, tnames[it - 1], root)
+        cost, g, _ = net.loss_and_grads(p, torch.from_numpy(x), t, e.numLayers, e.channelSize)
+        avg = cost if avg is None else avg
+        avg = .95 * avg + .05 * cost
+        if it % 10 == 0:
+            if it % e.validation_interval == 0:
+                vwant.append(net.eval_validation(p, torch.from_numpy(vx), vt, B, e.numLayers, e.channelSize)[0])
+            want.append(avg)
+        rate = net.sgd_step(p, g, rate, e.rateDecay)
+    assert len(costs) == 3 and len(vcosts) == 1
+    assert np.allclose(costs, want, atol=2e-4), (costs, want)
+    assert abs(vcosts[0] - vwant[0]) < 2e-4
+    assert abs(e.optimizer.rate - rate) < 1e-15
+    assert np.abs(e.modelParameters.numpy() - p.numpy()).max() < 1e-4
+    assert out.count("training ") == 2 and out.count("validation at iteration 20") == 1        # print cadence, train.lua:117-127
+
+
+@pytest.mark.gpu
+def test_checkpoint_resume_and_repeated_run(host, tmp_path, capsys):
+    """experiment:save / Experiment:load (experiments.lua:124-131) and experiments/repeated.lua: reload the best model, fresh
+    SGD.new(rate, rateDecay), run more iterations."""
+    import random
+    from deepgo_b200.host import repeated
+    root = _make_tree(tmp_path)
+    e, flat = _experiment(host, root, tmp_path, precision=1)
+    random.seed(3)
+    e.run({"iters": 20, "base": str(root)})
+    assert os.path.exists("%s.model" % e.id)                  # saved at the validation of iteration 20 (train.lua:123)
+    fn = e.save(str(tmp_path / "best.model"))
+    e2 = host["experiments"].Experiment.load(fn)
+    assert e2.iterations == 20 and e2.numLayers == 3 and e2.channelSize == 64 and e2.batchSize == 4 and e2.validation_costs == e.validation_costs
+    assert np.array_equal(e2.modelParameters.numpy(), e.modelParameters.numpy())
+    assert e2.optimizer.rate == e.optimizer.rate and e2.optimizer.rate < 0.05
+    r, _ = repeated.repeated(fn, gpu=1, num=7, iters=10, base=str(root))
+    assert r.id == "repeatedRun7" and r.iterations == 30
+    assert abs(r.optimizer.rate - 0.05 * (1 - 1e-7) ** 10) < 1e-15          # the loaded run's decayed rate was dropped (repeated.lua:17)
+    assert "experiment rate 0.05" in capsys.readouterr().out
+    assert not np.array_equal(r.modelParameters.numpy(), e.modelParameters.numpy())
+    # a checkpoint in the reference's own format goes through the same door
+    from tests.test_checkpoint import write_reference_model
+    ref_fn = tmp_path / "ref.model"
+    write_reference_model(ref_fn, e.modelParameters.numpy(), "Cuda", 0.004, 1e-7, 1234)
+    e3 = host["experiments"].Experiment.load(str(ref_fn), data_root=str(root / "data"), precision=1)
+    assert e3.iterations == 1234 and e3.optimizer.rate == 0.004 and np.array_equal(e3.modelParameters.numpy(), e.modelParameters.numpy())
