@@ -14,7 +14,7 @@ ROOT = _os.path.dirname(_PKG)
 HEADER = _os.path.join(ROOT, "include", "deepgo.h")
 LIB_PATH = _os.path.join(_PKG, "libdeepgo_b200.so")
 
-DG_PREC_FP32, DG_PREC_BF16 = 0, 1
+DG_PREC_FP32, DG_PREC_BF16, DG_PREC_TF32 = 0, 1, 2
 DG_FMT_F32_NCHW, DG_FMT_BITPLANES = 0, 1
 
 

@@ -270,7 +270,7 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     DG_REQUIRE(channel_size >= 1 && max_batch >= 1, "dg_model_create: bad channelSize/max_batch");
     DG_REQUIRE(k_first == 3 || k_first == 5, "dg_model_create: first kernel must be 3 or 5");
     DG_REQUIRE(in_planes == DG_PLANES, "dg_model_create: in_planes must be %d (dataloader.lua TOTAL)", DG_PLANES);
-    DG_REQUIRE(precision == DG_PREC_FP32 || precision == DG_PREC_BF16, "dg_model_create: unknown precision %d", precision);
+    DG_REQUIRE(precision == DG_PREC_FP32 || precision == DG_PREC_BF16 || precision == DG_PREC_TF32, "dg_model_create: unknown precision %d", precision);
     if (!c->kids.empty()) return dgm_model_create(c, num_layers, channel_size, in_planes, k_first, precision, max_batch, out);
     DG_CUDA(cudaSetDevice(c->dev));
     dg_model *m = new dg_model();
@@ -300,6 +300,11 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     if (precision == DG_PREC_FP32) {
         for (int l = 0; l < num_layers; ++l) DG_CUDA(cudaMalloc(&m->act[l + 1], B * m->layers[l].cout * DG_POINTS * 4));
         for (int i = 0; i < 2; ++i) DG_CUDA(cudaMalloc(&m->dz[i], B * channel_size * DG_POINTS * 4));
+    } else if (precision == DG_PREC_TF32) {
+        // the fp32 head works on NCHW maps: h_{L-1}, the 1-channel output map, and the two gradient maps around the head layer
+        for (int l = num_layers - 1; l <= num_layers; ++l) DG_CUDA(cudaMalloc(&m->act[l], B * m->layers[l - 1].cout * DG_POINTS * 4));
+        for (int i = 0; i < 2; ++i) DG_CUDA(cudaMalloc(&m->dz[i], B * channel_size * DG_POINTS * 4));
+        if (int rc = dg_tf32_create(m)) { return rc; }
     } else {
         if (int rc = dg_bf16_create(m)) { return rc; }
     }
@@ -313,6 +318,7 @@ extern "C" int dg_model_destroy(dg_model *m) {
     cudaSetDevice(m->ctx->dev);
     cudaStreamSynchronize(m->ctx->stream);
     if (m->bf) dg_bf16_destroy(m);
+    if (m->t32) dg_tf32_destroy(m);
     for (float *p : m->act) if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) if (m->dz[i]) cudaFree(m->dz[i]);
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
@@ -340,6 +346,7 @@ extern "C" int dg_model_set_params(dg_model *m, const float *host, size_t n) {
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     DG_CUDA(cudaMemcpyAsync(m->params, host, n * 4, cudaMemcpyHostToDevice, m->ctx->stream));
     if (m->bf) if (int rc = dg_bf16_params_changed(m)) return rc;
+    if (m->t32) if (int rc = dg_tf32_params_changed(m)) return rc;
     DG_CUDA(cudaStreamSynchronize(m->ctx->stream));
     return 0;
 }
@@ -423,9 +430,9 @@ extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uin
     }
     if (x) {
         // the bf16 path's encode kernel computes the labels as well (one launch less per batch)
-        if (m->prec == DG_PREC_FP32 || dg_bf16_input_mode_fused()) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
+        if (m->prec != DG_PREC_BF16 || dg_bf16_input_mode_fused()) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
     }
-    if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]);
+    if (m->prec != DG_PREC_BF16) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]);
     return dg_bf16_stage_raw(m);
 }
 
@@ -436,8 +443,8 @@ extern "C" int dg_model_encode_resident(dg_model *m) {
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
     m->forward_done = false;
-    if (m->have_targets && (m->prec == DG_PREC_FP32 || dg_bf16_input_mode_fused())) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, m->n, m->d_targets)) return rc;
-    if (m->prec == DG_PREC_FP32) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, m->n, m->act[0]);
+    if (m->have_targets && (m->prec != DG_PREC_BF16 || dg_bf16_input_mode_fused())) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, m->n, m->d_targets)) return rc;
+    if (m->prec != DG_PREC_BF16) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, m->n, m->act[0]);
     return dg_bf16_stage_raw(m);
 }
 
@@ -472,6 +479,13 @@ int dg_forward_impl(dg_model *m) {
         }
         if (int rc = dg_launch_logsoftmax_nll(c, m->act[m->L], m->have_targets ? m->d_targets : nullptr, m->d_logp, m->d_loss_n,
                                               nullptr, m->d_argmax, m->n, 0.f)) return rc;
+    } else if (m->prec == DG_PREC_TF32) {
+        if (int rc = dg_tf32_forward(m)) return rc;
+        const LayerInfo &lh = m->layers[m->L - 1];
+        if (int rc = dg_simt_conv(c, m->act[m->L - 1], m->params + lh.offW, m->params + lh.offB, m->params + lh.offA, nullptr,
+                                  m->act[m->L], m->n, lh.cin, lh.cout, lh.k, 0, 1)) return rc;
+        if (int rc = dg_launch_logsoftmax_nll(c, m->act[m->L], m->have_targets ? m->d_targets : nullptr, m->d_logp, m->d_loss_n,
+                                              nullptr, m->d_argmax, m->n, 0.f)) return rc;
     } else {
         if (int rc = dg_bf16_forward(m)) return rc;
     }
@@ -486,6 +500,17 @@ int dg_backward_impl(dg_model *m) {
     DG_REQUIRE(m->have_targets, "backward: the staged batch has no targets");
     const float scale = grad_scale(m);
     if (m->prec == DG_PREC_BF16) return dg_bf16_backward(m, scale);
+    if (m->prec == DG_PREC_TF32) {
+        // the 1-channel head layer on the fp32 kernels, then the conv stack on the tensor cores
+        const LayerInfo &lh = m->layers[m->L - 1];
+        if (int rc = dg_launch_logsoftmax_nll(c, m->act[m->L], m->d_targets, m->d_logp, m->d_loss_n, m->dz[1], m->d_argmax, m->n, scale)) return rc;
+        if (int rc = dg_simt_bias_grad(c, m->dz[1], m->grads + lh.offA, m->grads + lh.offB, m->n, lh.cout)) return rc;
+        if (int rc = dg_simt_wgrad(c, m->act[m->L - 1], m->dz[1], m->grads + lh.offW, m->n, lh.cin, lh.cout, lh.k)) return rc;
+        if (int rc = dg_simt_conv(c, m->dz[1], m->params + lh.offW, nullptr, nullptr, m->act[m->L - 1], m->dz[0], m->n, lh.cout, lh.cin, lh.k, 1, 0)) return rc;
+        if (int rc = dg_tf32_backward(m, m->dz[0])) return rc;
+        if (m->fused_step) if (int rc = dg_dp_bucket(c, m->grads, m->P)) return rc;
+        return 0;
+    }
     int cur = 0;
     if (int rc = dg_launch_logsoftmax_nll(c, m->act[m->L], m->d_targets, m->d_logp, m->d_loss_n, m->dz[cur], m->d_argmax, m->n, scale)) return rc;
     for (int l = m->L - 1; l >= 0; --l) {
@@ -539,7 +564,9 @@ extern "C" int dg_sgd_step(dg_model *m, float rate) {
     if (DG_MULTI(m)) return dgm_sgd_step(m, rate);
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (m->bf) { if (int rc = dg_bf16_sync_grads(m)) return rc; return dg_bf16_sgd_step(m, rate, nullptr); }
-    return dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate);
+    if (int rc = dg_launch_sgd(m->ctx, m->params, m->grads, m->P, rate)) return rc;
+    if (m->t32) return dg_tf32_params_changed(m);
+    return 0;
 }
 
 // one fused step on the context's stream: eval() of train.lua:4-12 followed by SGD:step (train.lua:131)

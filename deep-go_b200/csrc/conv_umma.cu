@@ -883,10 +883,6 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float *__restri
     }
 }
 
-struct FinalizeLayer {
-    const float *gacc; float *gW; int cin_true, cin, cout, ksize;
-    const float *gab; float *ga, *gb; int pitch, pad, first;      // bias gradients accumulated by the weight-gradient kernel (gab may be NULL)
-};
 
 // gW[(co*cin_true + ci)*KK + t] += gacc[t][ci/4][co][ci%4].  blockIdx.y selects the layer (one launch for the whole net).  A tile is
 // (co_t output channels) x (16 input channels) x ALL taps: the accumulation buffer is read with co-fastest 16-byte loads, and
@@ -952,6 +948,14 @@ __global__ void __launch_bounds__(256) wgrad_finalize_kernel(const FinalizeLayer
         }
     }
     DG_TL_OUT(tl, DG_TL_FINALIZE);
+}
+
+int dg_launch_wgrad_finalize(dg_ctx *c, const FinalizeLayer *table_dev, int nlayers, cudaStream_t st) {
+    dg_prof_scope _ps(c, DG_K_WGRAD_REDUCE, st);
+    wgrad_finalize_kernel<<<dim3(96, nlayers), 256, FIN_SMEM_FLOATS * 4, st>>>(table_dev, nullptr);
+    c->launches++;
+    DG_CUDA(cudaGetLastError());
+    return 0;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1903,14 +1907,14 @@ static int launch_conv(dg_model *m, ConvParams cp) {
 
 struct WgradPlan { int nb, n_mblk, n_nblk, combos, splits, nstages, rp; size_t smem, scratch_bytes; };
 
-static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const Geom &g, WgradPlan &w) {
+static int wgrad_plan(int num_sms, int cin_pad, int cout, int ksize, const Geom &g, WgradPlan &w) {
     w.nb = cin_pad;
     while (ksize * w.nb > 512) w.nb /= 2;
     DG_REQUIRE(w.nb % 16 == 0 && cin_pad % w.nb == 0 && w.nb <= 256, "bf16 path: unsupported weight-gradient N block for cin %d", cin_pad);
     w.n_nblk = cin_pad / w.nb;
     w.n_mblk = (cout + 127) / 128;
     w.combos = ksize * w.n_mblk * w.n_nblk;
-    DG_REQUIRE(w.combos <= m->bf->num_sms, "bf16 path: too many weight-gradient tiles");
+    DG_REQUIRE(w.combos <= num_sms, "bf16 path: too many weight-gradient tiles");
     // a multiple of the panels per position: every CTA then sees one panel index only (its bias-gradient accumulator is one panel)
     // K rows per ring stage.  96 (four 50 KB stages instead of three 65 KB ones, DG_WG_RP96=1) was measured: no gain, the producer
     // then issues a third more copies per byte and the units no longer divide evenly among the CTAs
@@ -1918,7 +1922,7 @@ static int wgrad_plan(const dg_model *m, int cin_pad, int cout, int ksize, const
     w.rp = (g.ntiles * 128) % 96 == 0 && rp96 ? 96 : 128;
     const int WG_RP = w.rp;
     const int panels = g.ntiles * 128 / WG_RP;
-    w.splits = m->bf->num_sms / w.combos;
+    w.splits = num_sms / w.combos;
     if (w.splits > panels) w.splits -= w.splits % panels;
     const int rb_pad = (WG_RP + 2 * g.pad + 7) & ~7;
     const size_t stage = 16 * WG_RP * 16 + (size_t)(w.nb / 8) * rb_pad * 16;
@@ -1966,7 +1970,7 @@ int dg_bf16_create(dg_model *m) {
         if (l > 0) if (int rc = alloc0((void **)&o.wd, nw * 2)) return rc;
         if (int rc = alloc0((void **)&o.ab, (size_t)li.cout * DG_R3 * 2)) return rc;
         WgradPlan w;
-        if (int rc = wgrad_plan(m, o.cin_pad, li.cout, li.k, l == 0 ? b->g_first : b->g3, w)) return rc;
+        if (int rc = wgrad_plan(b->num_sms, o.cin_pad, li.cout, li.k, l == 0 ? b->g_first : b->g3, w)) return rc;
         if (w.scratch_bytes > scratch) scratch = w.scratch_bytes;
     }
     {
@@ -2023,7 +2027,7 @@ int dg_bf16_create(dg_model *m) {
     for (int l = 0; l < L - 1; ++l) {
         const Geom &gl = l == 0 ? b->g_first : b->g3;
         WgradPlan wpl;
-        if (int rc = wgrad_plan(m, b->ops[l].cin_pad, m->layers[l].cout, m->layers[l].k, gl, wpl)) return rc;
+        if (int rc = wgrad_plan(b->num_sms, b->ops[l].cin_pad, m->layers[l].cout, m->layers[l].k, gl, wpl)) return rc;
         if (m->layers[l].k * wpl.nb + wpl.rp > 512 || wpl.splits % (gl.ntiles * 128 / wpl.rp) != 0) b->fused_bias = false;
         b->gacc_off[l] = b->gacc_floats; b->gacc_floats += (size_t)m->layers[l].k * m->layers[l].k * b->ops[l].cin_pad * m->layers[l].cout;
         b->gab_off[l] = b->gacc_floats; b->gacc_floats += (size_t)gl.ntiles * 128 * m->layers[l].cout;
@@ -2140,6 +2144,32 @@ int dg_bf16_dp_prepare(dg_model *m) {
     // pull mode (DG_DP_PULL=1: reduce-scatter only, the SGD kernel fetches each slice from its owner) is implemented and tested but
     // slower: remote reads inside the latency-bound SGD blocks cost 27 us, the write phase it saves 4 us (2 GPUs)
     b->p2p_pull = b->p2p != nullptr && getenv("DG_DP_PULL") != nullptr;
+    return 0;
+}
+
+// One layer's weight gradient with the bf16 tensor-core kernel, for callers outside this path (conv_tf32.cu feeds it hi/lo splits of
+// fp32 images): dz [n][cout/8][R][8], x [n][cin_pad/8][R][8] in the geometry of a k x k layer, partial tiles ADDED into
+// gacc [tap][cin_pad/4][cout][4].
+int dg_bf16_wgrad_single(dg_ctx *c, int num_sms, const void *dz, const void *x, float *gacc, int n, int cin_pad, int cout, int ksize) {
+    const Geom g = geom_for(ksize);
+    WgradPlan w;
+    if (int rc = wgrad_plan(num_sms, cin_pad, cout, ksize, g, w)) return rc;
+    static bool attr_set[64] = {false};
+    if (c->dev < 64 && !attr_set[c->dev]) {
+        DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+        attr_set[c->dev] = true;
+    }
+    WgradParams wp{};
+    wp.dz[0] = (const bf16 *)dz; wp.x[0] = (const bf16 *)x; wp.gacc[0] = gacc; wp.gab[0] = nullptr;
+    wp.scratch = nullptr; wp.nl = 1;
+    wp.n = n; wp.cin = cin_pad; wp.cout = cout;
+    wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = ksize; wp.first = g.first; wp.ntiles = g.ntiles;
+    wp.ngroups = 1;
+    wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
+    DG_REQUIRE(w.rp == 128, "weight gradient: 128-row stages expected");
+    { dg_prof_scope _ps(c, DG_K_WGRAD);
+    DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<128>, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp)); }
+    c->launches++;
     return 0;
 }
 
@@ -2324,7 +2354,7 @@ int dg_bf16_backward(dg_model *m, float scale) {
         const LayerInfo &li = m->layers[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
         WgLaunch q; q.l = l;
-        if (int rc = wgrad_plan(m, b->ops[l].cin_pad, li.cout, li.k, g, q.w)) return rc;
+        if (int rc = wgrad_plan(b->num_sms, b->ops[l].cin_pad, li.cout, li.k, g, q.w)) return rc;
         q.nl = 1;
         if (!b->deterministic && l >= 1) q.nl = std::min(l, WG_MAX_LAYERS);       // layers l, l-1, .., l-nl+1 (all >= 1)
         const int panels_l = g.ntiles * 128 / q.w.rp;

@@ -3,6 +3,15 @@
 #include "common.cuh"
 
 struct Bf16Path;   // conv_umma.cu
+struct Tf32Path;   // conv_tf32.cu
+
+// one layer of the launch that folds weight-gradient accumulation blocks [tap][cin/4][cout][4] into the Torch7-order gradient
+struct FinalizeLayer {
+    const float *gacc; float *gW; int cin_true, cin, cout, ksize;
+    const float *gab; float *ga, *gb; int pitch, pad, first;      // bias gradients accumulated by the weight-gradient kernel (gab may be NULL)
+};
+int dg_bf16_wgrad_single(dg_ctx *c, int num_sms, const void *dz_bf16, const void *x_bf16, float *gacc, int n, int cin_pad, int cout, int ksize);   // conv_umma.cu
+int dg_launch_wgrad_finalize(dg_ctx *ctx, const FinalizeLayer *table_dev, int nlayers, cudaStream_t st);    // conv_umma.cu
 
 struct dg_model {
     dg_ctx *ctx = nullptr;
@@ -39,6 +48,8 @@ struct dg_model {
     float *dz[2] = {nullptr, nullptr};
     // bf16 tcgen05 path
     Bf16Path *bf = nullptr;
+    // tf32 tcgen05 path
+    Tf32Path *t32 = nullptr;
     // model on a multi-device context: one replica per device, the staged batch split on dim 0 (multi.cu)
     std::vector<dg_model *> kids;
     std::vector<int> kid_lo;           // first position of the staged batch on replica k
@@ -51,6 +62,13 @@ int dg_forward_impl(dg_model *m);
 int dg_backward_impl(dg_model *m);
 int dg_read_loss(dg_model *m, float *loss_out, int *errors_out);
 int dg_bf16_dp_prepare_local(dg_model *const *kids, int n);   // conv_umma.cu
+
+// conv_tf32.cu
+int dg_tf32_create(dg_model *m);
+void dg_tf32_destroy(dg_model *m);
+int dg_tf32_params_changed(dg_model *m);                 // refresh the fp32 operand copies from the master
+int dg_tf32_forward(dg_model *m);                        // conv layers 0 .. L-2; leaves h_{L-1} (NCHW) in act[L-1]
+int dg_tf32_backward(dg_model *m, const float *dz_top);  // dz_top: dZ of conv layer L-2, NCHW; gradients of the conv layers into m->grads
 
 // conv_umma.cu
 int dg_bf16_create(dg_model *m);

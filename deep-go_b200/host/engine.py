@@ -3,7 +3,7 @@ libdeepgo_b200.so; nothing here computes."""
 import numpy as np
 
 import deepgo_b200 as _dg
-from deepgo_b200 import ffi, check, DG_PREC_FP32, DG_PREC_BF16, DG_FMT_F32_NCHW, DG_FMT_BITPLANES  # noqa: F401
+from deepgo_b200 import ffi, check, DG_PREC_FP32, DG_PREC_BF16, DG_PREC_TF32, DG_FMT_F32_NCHW, DG_FMT_BITPLANES  # noqa: F401
 
 
 KERNEL_KINDS = ["encode", "conv_first", "conv", "dgrad", "wgrad", "wgrad_reduce", "bias_grad", "head", "sgd", "pack",

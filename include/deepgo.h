@@ -30,7 +30,10 @@ typedef struct dg_ctx dg_ctx;
 typedef struct dg_model dg_model;
 
 /* precision of the conv stack */
-enum { DG_PREC_FP32 = 0, DG_PREC_BF16 = 1 };
+/* FP32: CUDA cores, the reference's CUDA arithmetic (train.lua:99-100); BF16: tcgen05 kind::f16 with bf16 operands and stored
+ * activations, fp32 accumulation -- the fast path; TF32: tcgen05 kind::tf32, fp32 storage, 10-bit-mantissa products, fp32
+ * accumulation -- the tensor-core type closest to the reference's */
+enum { DG_PREC_FP32 = 0, DG_PREC_BF16 = 1, DG_PREC_TF32 = 2 };
 /* output formats of dg_encode */
 enum { DG_FMT_F32_NCHW = 0, DG_FMT_BITPLANES = 1 };
 

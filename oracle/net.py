@@ -10,7 +10,9 @@ module semantics at the reference's call sites:
 It is self-checked by autograd + finite differences in tests/test_oracle_net.py.
 
 `quant="bf16"` rounds the same tensors the B200 bf16 path rounds (weights, stored activations h_l,
-stored dZ_l) so the GPU can be compared tightly; `quant=None` is the reference fp64 arithmetic.
+stored dZ_l) so the GPU can be compared tightly; `quant="tf32"` does the same for the TF32 path (weight operands, stored
+activations and stored dZ rounded to 10 mantissa bits; bias and sums in full precision); `quant=None` is the reference
+fp64 arithmetic.
 """
 import math
 import numpy as np
@@ -67,6 +69,12 @@ def init_params(num_layers, channel_size, seed, kind="torch7", dtype=torch.float
 def _q(t, quant):
     if quant == "bf16":
         return t.to(torch.bfloat16).to(t.dtype)
+    if quant == "tf32":
+        # round to nearest, ties away from zero, to 10 mantissa bits (cvt.rna.tf32.f32): add half an ulp of the kept part to the
+        # magnitude and clear the 13 dropped bits
+        i = t.to(torch.float32).contiguous().view(torch.int32)
+        i = (i + 0x1000) & ~0x1FFF
+        return i.view(torch.float32).to(t.dtype)
     return t
 
 
@@ -80,10 +88,10 @@ def forward(flat, x, num_layers, channel_size, quant=None):
         k = W.shape[-1]
         Wq = _q(W, quant) if i < len(layers) - 1 else W         # the 1-channel head keeps fp32 weights on the GPU
         bias = b.view(-1, 1, 1) + a                               # per-channel + per-point bias (experiments.lua:138,143-145)
-        if i < len(layers) - 1:
+        if i < len(layers) - 1 and quant == "bf16":
             bias = _q(bias, quant)                                # the GPU's bf16 epilogue operand; the head keeps fp32
         z = F.conv2d(h, Wq, None, padding=(k - 1) // 2)
-        if i < len(layers) - 1:
+        if i < len(layers) - 1 and quant == "bf16":
             z = _q(z, quant)                                      # the GPU rounds the fp32 accumulator to bf16, then adds the
         z = z + bias.unsqueeze(0)                                 # bf16 bias with one more rounding (packed fma + ReLU)
         zs.append(z)
