@@ -1503,34 +1503,48 @@ __global__ void __launch_bounds__(256) head_grad_reduce_kernel(const float *__re
 // ---------------------------------------------------------------------------------------------
 
 // raw records -> blocked bf16 input image [n][48/8][R][8] (planes 37..47 stay zero); same plane
-// definitions as encode.cu (dataloader.lua:50-92)
-__global__ void __launch_bounds__(384) encode_blocked_kernel(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ player,
+// definitions as encode.cu (dataloader.lua:50-92).  One block per position:
+//   * the 3,249-byte record is pulled into shared memory with 16-byte loads (records are odd-sized, so the block reads the aligned
+//     window around its record; the window's last 16 bytes are fetched byte-wise where they would cross the end of the buffer);
+//   * one thread per IMAGE ROW from the first to the last board point, pad rows included (they are written as zeros, which they
+//     already are): every channel chunk is then ONE contiguous run of 16-byte stores, whole 32-byte sectors throughout, instead of
+//     19-row runs with 2-row holes whose edge sectors are partial writes.
+__global__ void __launch_bounds__(512) encode_blocked_kernel(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ player,
                                                             const uint8_t *__restrict__ rank, const uint8_t *__restrict__ sym,
                                                             bf16 *__restrict__ out, int R, int pitch, int pad,
-                                                            const uint8_t *__restrict__ mx, const uint8_t *__restrict__ my, int32_t *__restrict__ targets) {
-    const int n = blockIdx.x, p = threadIdx.x;
+                                                            const uint8_t *__restrict__ mx, const uint8_t *__restrict__ my, int32_t *__restrict__ targets,
+                                                            size_t raw_bytes) {
+    __shared__ __align__(16) uint8_t rec_s[DG_RAW_PLANES * DG_POINTS + 32];
+    const int n = blockIdx.x, tid = threadIdx.x;
     dg_pdl_launch_dependents();
     dg_pdl_wait();
-    if (p == DG_POINTS && targets) {
+    const size_t base = (size_t)n * DG_RAW_PLANES * DG_POINTS, abase = base & ~(size_t)15;
+    const int shift = (int)(base - abase);
+    const int nvec = (shift + DG_RAW_PLANES * DG_POINTS + 15) >> 4;
+    for (int v = tid; v < nvec; v += blockDim.x) {
+        const size_t off = abase + (size_t)v * 16;
+        if (off + 16 <= raw_bytes) *reinterpret_cast<uint4 *>(rec_s + v * 16) = __ldg(reinterpret_cast<const uint4 *>(raw + off));
+        else for (int e = 0; e < 16; ++e) rec_s[v * 16 + e] = off + e < raw_bytes ? raw[off + e] : 0;
+    }
+    const int sy = sym ? sym[n] : 0;
+    if (tid == 511 && targets) {
         // the move label of the position (dataloader.lua:89), transformed like the board: saves the separate labels launch
         int a = mx[n] - 1, b = my[n] - 1;
-        const int sy = sym ? sym[n] : 0;
         if (sy & 1) { int t = a; a = b; b = t; }
         if (sy & 2) a = DG_BOARD - 1 - a;
         if (sy & 4) b = DG_BOARD - 1 - b;
         targets[n] = DG_BOARD * a + b;
     }
-    if (p >= DG_POINTS) return;
-    const int src = dg_src_point_d(p, sym ? sym[n] : 0);
-    const uint8_t *rec = raw + (size_t)n * DG_RAW_PLANES * DG_POINTS;
     const int pl = player[n], rk = rank[n];
-    const unsigned long long m = dg_plane_bits(rec, src, pl, rk);
-    const int x = p / DG_BOARD, y = p - x * DG_BOARD;
-    const int rho = (x + pad) * pitch + y + pad;
+    __syncthreads();
+    const int row_first = pad * pitch + pad, row_last = (DG_BOARD - 1 + pad) * pitch + DG_BOARD - 1 + pad;
+    for (int rho = row_first + tid; rho <= row_last; rho += blockDim.x) {
+        const int xp = rho / pitch, yp = rho - xp * pitch;
+        const int x = xp - pad, y = yp - pad;
+        unsigned long long m = 0;
+        if (y >= 0 && y < DG_BOARD) m = dg_plane_bits(rec_s + shift, dg_src_point_d(x * DG_BOARD + y, sy), pl, rk);      // x is on the board for every row in range
 #pragma unroll
-    for (int c = 0; c < 6; ++c) {
-        const uint4 o = dg_plane_chunk(m, c);
-        *reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8) = o;
+        for (int c = 0; c < 6; ++c) *reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8) = dg_plane_chunk(m, c);
     }
 }
 
@@ -2232,8 +2246,8 @@ int dg_bf16_stage_raw(dg_model *m) {
     if (fused && b->ops[0].cin_pad == 48) { b->x0_from_raw = true; return 0; }
     b->x0_from_raw = false;
     { dg_prof_scope _ps(c, DG_K_ENCODE);
-    DG_CUDA(dg_launch_pdl(encode_blocked_kernel, dim3(m->n), dim3(384), 0, c->stream, (const uint8_t *)m->d_raw, (const uint8_t *)m->d_player, (const uint8_t *)m->d_rank, (const uint8_t *)m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad,
-                          (const uint8_t *)m->d_x, (const uint8_t *)m->d_y, m->have_targets ? m->d_targets : (int32_t *)nullptr));
+    DG_CUDA(dg_launch_pdl(encode_blocked_kernel, dim3(m->n), dim3(512), 0, c->stream, (const uint8_t *)m->d_raw, (const uint8_t *)m->d_player, (const uint8_t *)m->d_rank, (const uint8_t *)m->d_sym, b->x0, b->g_first.rows, b->g_first.pitch, b->g_first.pad,
+                          (const uint8_t *)m->d_x, (const uint8_t *)m->d_y, m->have_targets ? m->d_targets : (int32_t *)nullptr, (size_t)m->max_batch * DG_RAW_PLANES * DG_POINTS));
     }
     c->launches++;
     DG_CUDA(cudaGetLastError());
