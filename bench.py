@@ -350,7 +350,7 @@ def run_ours(args, rank, local_rank, world):
     value = BATCH * world / (ms_per_step * 1e-3)
     # the round-1 way, for comparison: every step timed on its own, an untimed 256 MB fill before it (ranks drift apart during the
     # fill and the step's first cross-GPU barrier then waits for the slowest one inside the timed region)
-    fl_ms, _ = timed_steps(ctx, m, rate, args.steps, 0, barrier, nvml)
+    fl_ms, _ = timed_steps(ctx, m, rate, 1 if os.environ.get("DG_BENCH_NOFLUSH") else args.steps, 0, barrier, nvml)
     nvml.take()
     fl_ms = max_over_ranks(fl_ms) / args.steps
     flushed = {"ms_per_step": fl_ms, "positions_per_s": BATCH * world / (fl_ms * 1e-3),
@@ -362,10 +362,16 @@ def run_ours(args, rank, local_rank, world):
         m.set_batch_raw(pin["raw"], pin["player"], pin["rank"], pin["sym"], pin["x"], pin["y"]); m.train_step(rate)
     barrier()
     t0 = time.perf_counter()
+    dbg_t = []
     for _ in range(args.steps):
+        ta = time.perf_counter()
         m.set_batch_raw(pin["raw"], pin["player"], pin["rank"], pin["sym"], pin["x"], pin["y"])
+        tb = time.perf_counter()
         loss = m.train_step(rate)          # returns the step's loss: D2H read + sync inside
+        dbg_t.append((tb - ta, time.perf_counter() - tb))
     ctx.synchronize()
+    if os.environ.get("DG_BENCH_DEBUG"):
+        sys.stderr.write("[rank %d] e2e per step (set_batch us, train_step us): %s\n" % (rank, [(round(a * 1e6), round(c * 1e6)) for a, c in dbg_t]))
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = BATCH * world * args.steps / e2e_s
     h2d = BATCH * (9 * 361 + 5)
