@@ -251,6 +251,10 @@ def timed_region(ctx, m, rate, steps, warmup, barrier):
     for _ in range(warmup):
         m.encode_resident(); m.train_step(rate, want_loss=False)
     barrier()
+    # one more untimed step: at N > 1 its gradient exchange is a cross-GPU barrier ON THE DEVICE, so the ranks enter the timed
+    # region within microseconds of each other (hosts leave a torch.distributed barrier milliseconds apart now and then, and the
+    # first timed step would wait for the last one inside the region)
+    m.encode_resident(); m.train_step(rate, want_loss=False)
     lc = ctx.launch_count()
     ctx.timer_start()
     for _ in range(steps):
@@ -348,19 +352,13 @@ def run_ours(args, rank, local_rank, world):
     total_ms = max_over_ranks(total_ms)
     ms_per_step = total_ms / args.steps
     value = BATCH * world / (ms_per_step * 1e-3)
-    # the round-1 way, for comparison: every step timed on its own, an untimed 256 MB fill before it (ranks drift apart during the
-    # fill and the step's first cross-GPU barrier then waits for the slowest one inside the timed region)
-    fl_ms, _ = timed_steps(ctx, m, rate, 1 if os.environ.get("DG_BENCH_NOFLUSH") else args.steps, 0, barrier, nvml)
-    nvml.take()
-    fl_ms = max_over_ranks(fl_ms) / args.steps
-    flushed = {"ms_per_step": fl_ms, "positions_per_s": BATCH * world / (fl_ms * 1e-3),
-               "note": "per-step CUDA events, untimed 256 MB device fill between the steps"}
-
     # ---------------- end to end through the C ABI with host buffers ----------------
     pin = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy() for k, v in b.items()}
     for _ in range(3):
         m.set_batch_raw(pin["raw"], pin["player"], pin["rank"], pin["sym"], pin["x"], pin["y"]); m.train_step(rate)
     barrier()
+    for _ in range(2):      # untimed, after the barrier: the step's exchange aligns the ranks on the device, its loss read is the synchronize
+        m.set_batch_raw(pin["raw"], pin["player"], pin["rank"], pin["sym"], pin["x"], pin["y"]); m.train_step(rate)
     t0 = time.perf_counter()
     dbg_t = []
     for _ in range(args.steps):
@@ -398,6 +396,16 @@ def run_ours(args, rank, local_rank, world):
         ms4 = max_over_ranks(ms4) / steps4
         c4[name] = {"batch_per_gpu": per_gpu, "global_batch": per_gpu * world, "ms_per_step": ms4, "positions_per_s": per_gpu * world / (ms4 * 1e-3)}
         del m4
+
+    # ---------------- the round-1 way of timing, for comparison: every step on its own, an untimed 256 MB fill before it (ranks drift
+    # apart during the fill and the step's first cross-GPU barrier then waits for the slowest one inside the timed region).  After the
+    # headline measurements: after these fills the end-to-end loop showed millisecond stalls in single steps at N >= 4.
+    fl_ms, _ = timed_steps(ctx, m, rate, args.steps, 0, barrier, nvml)
+    nvml.take()
+    fl_ms = max_over_ranks(fl_ms) / args.steps
+    flushed = {"ms_per_step": fl_ms, "positions_per_s": BATCH * world / (fl_ms * 1e-3),
+               "note": "per-step CUDA events, untimed 256 MB device fill between the steps"}
+
 
     # ---------------- sustained: >= 2 s of back-to-back steps, no flush, no per-step sync (last of the timed parts: it heats the GPU into its power cap) ----------------
     n_sus = int(max(200, 2.4 / (ms_per_step * 1e-3)))
