@@ -476,7 +476,7 @@ def run_ours(args, rank, local_rank, world):
         roofline = {"kernel": "conv_umma_kernel (3x3, 128->128, forward, %g layers per launch)" % layers_per_launch, "bound": "tensor",
                     "achieved": achieved, "peak": burst, "unit": "TFLOP/s", "frac": achieved / burst, "traffic": ncu_traffic(),
                     "traffic_source": "static: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel "
-                                      "(profiles/roofline_traffic_r1.json), not re-measured by this run",
+                                      "(profiles/roofline_traffic_r2.json), not re-measured by this run",
                     "peak_source": peak_src + ", burst bf16 (kernel timed alone)", "avg_launch_ms": avg_ms, "flops_per_launch": flops,
                     "frac_of_sustained_peak": achieved / sustained}
     whole = F_TRAIN * BATCH / (ms_per_step * 1e-3) / 1e12
@@ -500,9 +500,9 @@ def run_ours(args, rank, local_rank, world):
 
 def ncu_traffic():
     """DRAM bytes (read + write) of one launch of the roofline kernel, from the committed `ncu --set full` capture
-    (profiles/roofline_traffic_r1.json: a measured constant of the kernel, not re-measured by the bench)."""
+    (profiles/roofline_traffic_r2.json: a measured constant of the kernel, not re-measured by the bench)."""
     try:
-        with open(os.path.join(ROOT, "profiles", "roofline_traffic_r1.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic_r2.json")) as f:
             return json.load(f)["dram_bytes_per_launch"]
     except (OSError, KeyError, ValueError):
         return None
