@@ -12,7 +12,7 @@ _PKG = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "deep-go_b200
     else _os.path.dirname(_os.path.abspath(__file__))
 ROOT = _os.path.dirname(_PKG)
 HEADER = _os.path.join(ROOT, "include", "deepgo.h")
-LIB_PATH = _os.path.join(_PKG, "libdeepgo_b200.so")
+LIB_PATH = _os.environ.get("DEEPGO_LIB") or _os.path.join(_PKG, "libdeepgo_b200.so")      # DEEPGO_LIB: as in lua/deepgo.lua
 
 DG_PREC_FP32, DG_PREC_BF16, DG_PREC_TF32 = 0, 1, 2
 DG_FMT_F32_NCHW, DG_FMT_BITPLANES = 0, 1

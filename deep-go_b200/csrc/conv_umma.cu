@@ -1794,7 +1794,8 @@ __global__ void __launch_bounds__(NT) sgd_pack_kernel(const SgdPackLayer *__rest
             for (int r = 0; r < CO_B; ++r) v[r] = __float2bfloat16(ci < L.cin_true ? wrow[r * smem_row + ci * KK + (KK - 1 - t)] : 0.f);
             bf16 *dst = L.wd + (((size_t)t * (L.cout >> 3) + (co0 >> 3)) * L.cin + ci) * 8 + (co0 & 7);
             if (CO_B == 8) *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(v);
-            else *reinterpret_cast<uint2 *>(dst) = *reinterpret_cast<const uint2 *>(v);
+            else if (CO_B == 4) *reinterpret_cast<uint2 *>(dst) = *reinterpret_cast<const uint2 *>(v);
+            else *reinterpret_cast<uint32_t *>(dst) = *reinterpret_cast<const uint32_t *>(v);
         }
     }
     DG_TL_OUT(tl, DG_TL_SGD);
