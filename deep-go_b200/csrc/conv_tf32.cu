@@ -60,8 +60,11 @@ struct T32Conv {
     int nb, kp, nstages, nimg, mode;
 };
 
-// 192 threads: warp 0 producer (bulk copies), warp 1 MMA issue + TMEM, warps 2..5 epilogue (TMEM lane quarter = warp % 4)
-__global__ void __launch_bounds__(192, 1) conv_tf32_kernel(const __grid_constant__ T32Conv p) {
+// 384 threads: warp 0 producer (bulk copies); warps 1, 10, 11 issue the MMAs, each for its own accumulator tile(s) (the tensor pipe's
+// queue is shallow: with a single issuing thread every barrier wait and commit shows up as a gap, see conv_umma.cu); warps 2..9
+// epilogue (TMEM lane quarter = warp % 4, two warps per quarter taking alternate 32-column blocks)
+#define T32_MMA_WARPS 3
+__global__ void __launch_bounds__(384, 1) conv_tf32_kernel(const __grid_constant__ T32Conv p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint64_t w_full[T32_MAX_STAGES], w_empty[T32_MAX_STAGES], img_full[2], img_empty[2], acc_full, acc_empty;
     __shared__ uint32_t tmem_base_s;
@@ -73,10 +76,10 @@ __global__ void __launch_bounds__(192, 1) conv_tf32_kernel(const __grid_constant
     uint8_t *ring = smem + (size_t)p.nimg * panel_pad;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], 1); }
-        mbar_init(&acc_full, 1);
-        mbar_init(&acc_empty, 4);
+        for (int s = 0; s < p.nstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], T32_MMA_WARPS); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&img_full[i], 1); mbar_init(&img_empty[i], T32_MMA_WARPS); }
+        mbar_init(&acc_full, T32_MMA_WARPS);
+        mbar_init(&acc_empty, 8);
         fence_barrier_init();
     }
     if (warp == 1) { tmem_alloc(&tmem_base_s, 512); tmem_relinquish(); }
@@ -105,14 +108,17 @@ __global__ void __launch_bounds__(192, 1) conv_tf32_kernel(const __grid_constant
                         if (elect_one()) {
                             mbar_arrive_expect_tx(&w_full[s], stage_bytes);
                             const uint8_t *wsrc = (const uint8_t *)p.w + (size_t)t * tap_stride + ((size_t)k * chunks_kp * p.cout + (size_t)nbk * p.nb) * 16;
-                            for (int c = 0; c < chunks_kp; ++c)
-                                bulk_g2s(ring + (size_t)s * stage_bytes + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
+                            if (nnb == 1) bulk_g2s(ring + (size_t)s * stage_bytes, wsrc, stage_bytes, &w_full[s]);      // one N block: the stage is one contiguous run
+                            else
+                                for (int c = 0; c < chunks_kp; ++c)
+                                    bulk_g2s(ring + (size_t)s * stage_bytes + (size_t)c * p.nb * 16, wsrc + (size_t)c * p.cout * 16, (uint32_t)p.nb * 16, &w_full[s]);
                         }
                         __syncwarp();
                         if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
                     }
                 }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp >= 10) {
+        const int mma_id = warp == 1 ? 0 : warp - 9;
         const uint32_t idesc = make_idesc_tf32(128, p.nb, 0, 0);
         const uint32_t hi = desc_hi(128);
         const int ksteps = p.kp >> 3;
@@ -131,7 +137,7 @@ __global__ void __launch_bounds__(192, 1) conv_tf32_kernel(const __grid_constant
                             tc_fence_after();
                             if (elect_one()) {
                                 const uint32_t b_lo_s = desc_lo(smem_u32(ring) + s * stage_bytes, (uint32_t)p.nb * 16);
-                                for (int tile = 0; tile < p.ntiles; ++tile) {
+                                for (int tile = mma_id; tile < p.ntiles; tile += T32_MMA_WARPS) {
                                     uint32_t a_lo = a_lo_k + (uint32_t)(ky * p.pitch_in + kx) + (uint32_t)tile * 128, b_lo = b_lo_s;
                                     for (int ks = 0; ks < ksteps; ++ks, a_lo += 2u * p.R_in, b_lo += 2u * p.nb)
                                         mma_tf32(tmem_base + (uint32_t)tile * p.nb, desc_join(a_lo, hi), desc_join(b_lo, hi), idesc, (uint32_t)((k | ky | kx | ks) != 0));
@@ -149,7 +155,7 @@ __global__ void __launch_bounds__(192, 1) conv_tf32_kernel(const __grid_constant
                 __syncwarp();
             }
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3, half = (warp - 2) >> 2;
         const uint32_t tm_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const int chunks_out = p.cout >> 2;
         uint32_t a = 0;
@@ -164,26 +170,34 @@ __global__ void __launch_bounds__(192, 1) conv_tf32_kernel(const __grid_constant
                     const bool valid = x >= 0 && x < DG_BOARD && y >= 0 && y < DG_BOARD;
                     const int rho_out = (x + p.pad_out) * p.pitch_out + y + p.pad_out;
                     const int rho_m = (x + p.pad_mask) * p.pitch_mask + y + p.pad_mask;
-                    for (int c0 = 0; c0 < p.nb; c0 += 32) {
+                    for (int c0 = half * 32; c0 < p.nb; c0 += 64) {          // nb is a multiple of 32
+                        const int chunk0 = (nbk * p.nb + c0) >> 2;
+                        // the eight bias (or mask) lines of the block are requested first, under the TMEM load: the drain is a chain of
+                        // L2 round trips otherwise
+                        float4 bm[8];
+                        if (valid) {
+                            const float4 *src = p.mode == 0 ? reinterpret_cast<const float4 *>(p.bias) + (size_t)chunk0 * p.R_out + rho_out
+                                                            : reinterpret_cast<const float4 *>(p.mask) + ((size_t)pos * chunks_out + chunk0) * p.R_mask + rho_m;
+                            const size_t stride = p.mode == 0 ? p.R_out : p.R_mask;
+#pragma unroll
+                            for (int g = 0; g < 8; ++g) bm[g] = __ldg(src + (size_t)g * stride);
+                        }
                         uint32_t r[32];
-                        if (p.nb - c0 >= 32) tmem_ld32(tm_lane + (uint32_t)tile * p.nb + c0, r); else tmem_ld16(tm_lane + (uint32_t)tile * p.nb + c0, r);
+                        tmem_ld32(tm_lane + (uint32_t)tile * p.nb + c0, r);
                         tmem_ld_wait();
                         if (!valid) continue;
-                        const int ncol = min(32, p.nb - c0);
+                        float4 *dst = reinterpret_cast<float4 *>(p.out) + ((size_t)pos * chunks_out + chunk0) * p.R_out + rho_out;
 #pragma unroll
                         for (int g = 0; g < 8; ++g) {
-                            if (g * 4 >= ncol) break;
-                            const int chunk = (nbk * p.nb + c0) / 4 + g;
                             float4 v = make_float4(__uint_as_float(r[g * 4]), __uint_as_float(r[g * 4 + 1]), __uint_as_float(r[g * 4 + 2]), __uint_as_float(r[g * 4 + 3]));
+                            const float4 b = bm[g];
                             if (p.mode == 0) {
-                                const float4 b = __ldg(reinterpret_cast<const float4 *>(p.bias) + (size_t)chunk * p.R_out + rho_out);
                                 v.x = fmaxf(v.x + b.x, 0.f); v.y = fmaxf(v.y + b.y, 0.f); v.z = fmaxf(v.z + b.z, 0.f); v.w = fmaxf(v.w + b.w, 0.f);
                             } else {
-                                const float4 mk = __ldg(reinterpret_cast<const float4 *>(p.mask) + ((size_t)pos * chunks_out + chunk) * p.R_mask + rho_m);
-                                v.x = mk.x > 0.f ? v.x : 0.f; v.y = mk.y > 0.f ? v.y : 0.f; v.z = mk.z > 0.f ? v.z : 0.f; v.w = mk.w > 0.f ? v.w : 0.f;
+                                v.x = b.x > 0.f ? v.x : 0.f; v.y = b.y > 0.f ? v.y : 0.f; v.z = b.z > 0.f ? v.z : 0.f; v.w = b.w > 0.f ? v.w : 0.f;
                             }
                             v.x = tf32_rna(v.x); v.y = tf32_rna(v.y); v.z = tf32_rna(v.z); v.w = tf32_rna(v.w);
-                            reinterpret_cast<float4 *>(p.out)[((size_t)pos * chunks_out + chunk) * p.R_out + rho_out] = v;
+                            dst[(size_t)g * p.R_out] = v;
                         }
                     }
                 }
@@ -323,7 +337,7 @@ struct Tf32Path {
     float *gacc = nullptr;                 // weight-gradient accumulation blocks [tap][cin/4][cout][4] of all conv layers
     std::vector<size_t> gacc_off;
     size_t gacc_floats = 0;
-    __nv_bfloat16 *dz_hi = nullptr, *dz_lo = nullptr, *x_hi = nullptr, *x_lo = nullptr;    // bf16 splits of one layer's dZ and X images
+    std::vector<__nv_bfloat16 *> dz_hi, dz_lo, x_hi, x_lo;      // bf16 hi / lo splits of every conv layer's dZ and X images
     T32Pack *pack_table = nullptr;
     FinalizeLayer *fin_table = nullptr;
     int num_sms = 148;
@@ -366,10 +380,12 @@ int dg_tf32_create(dg_model *m) {
         tab[l] = T32Pack{m->params + li.offW, m->params + li.offB, m->params + li.offA, b->wf[l], b->wd[l], b->ab[l], li.cin, cin_pad, li.cout, li.k};
     }
     DG_CUDA(cudaMalloc((void **)&b->gacc, b->gacc_floats * 4));
-    {
-        const size_t img = B * (size_t)std::max(C, b->cin0_pad) * std::max(b->g_first.rows, T32_R3) * 2;
-        DG_CUDA(cudaMalloc((void **)&b->dz_hi, img)); DG_CUDA(cudaMalloc((void **)&b->dz_lo, img));
-        DG_CUDA(cudaMalloc((void **)&b->x_hi, img)); DG_CUDA(cudaMalloc((void **)&b->x_lo, img));
+    b->dz_hi.assign(L - 1, nullptr); b->dz_lo.assign(L - 1, nullptr); b->x_hi.assign(L - 1, nullptr); b->x_lo.assign(L - 1, nullptr);
+    for (int l = 0; l < L - 1; ++l) {
+        const size_t R = l == 0 ? b->g_first.rows : T32_R3;
+        const size_t dzb = B * (size_t)C * R * 2, xb = B * (size_t)(l == 0 ? b->cin0_pad : C) * R * 2;
+        DG_CUDA(cudaMalloc((void **)&b->dz_hi[l], dzb)); DG_CUDA(cudaMalloc((void **)&b->dz_lo[l], dzb));
+        DG_CUDA(cudaMalloc((void **)&b->x_hi[l], xb)); DG_CUDA(cudaMalloc((void **)&b->x_lo[l], xb));
     }
     for (int l = 0; l < L - 1; ++l) {
         const LayerInfo &li = m->layers[l];
@@ -397,7 +413,7 @@ void dg_tf32_destroy(dg_model *m) {
     for (float *p : b->wd) if (p) cudaFree(p);
     for (float *p : b->ab) if (p) cudaFree(p);
     cudaFree(b->gacc); cudaFree(b->pack_table); cudaFree(b->fin_table);
-    cudaFree(b->dz_hi); cudaFree(b->dz_lo); cudaFree(b->x_hi); cudaFree(b->x_lo);
+    for (auto *v : {&b->dz_hi, &b->dz_lo, &b->x_hi, &b->x_lo}) for (__nv_bfloat16 *p : *v) if (p) cudaFree(p);
     delete b;
     m->t32 = nullptr;
 }
@@ -426,7 +442,7 @@ static int t32_launch_conv(dg_model *m, T32Conv cp) {
     const size_t smem = cp.nimg * panel + cp.nstages * stage;
     const int grid = std::min(cp.n, m->t32->num_sms);
     { dg_prof_scope _ps(c, cp.mode ? DG_K_DGRAD : (cp.ksize == 5 ? DG_K_CONV_FIRST : DG_K_CONV));
-    conv_tf32_kernel<<<grid, 192, smem, c->stream>>>(cp); }
+    conv_tf32_kernel<<<grid, 384, smem, c->stream>>>(cp); }
     c->launches++;
     DG_CUDA(cudaGetLastError());
     return 0;
@@ -476,17 +492,6 @@ int dg_tf32_backward(dg_model *m, const float *dz_top) {
             t32_bias_grad_kernel<<<dim3(li.cout / 4, groups), 384, 0, c->stream>>>(b->dzl[l], m->grads + li.offA, m->grads + li.offB, m->n, li.cout, g.rows, g.pitch, g.pad, groups);
             c->launches++;
         }
-        {   // weight gradient: bf16 hi/lo splits, three tensor-core products (see above)
-            const float *xl = l == 0 ? b->x0 : b->h[l];
-            const size_t rows_dz = (size_t)m->n * (li.cout / 8) * g.rows, rows_x = (size_t)m->n * (cin_pad / 8) * g.rows;
-            t32_split_bf16_kernel<<<2 * b->num_sms, 256, 0, c->stream>>>(b->dzl[l], b->dz_hi, b->dz_lo, rows_dz, g.rows);
-            t32_split_bf16_kernel<<<2 * b->num_sms, 256, 0, c->stream>>>(xl, b->x_hi, b->x_lo, rows_x, g.rows);
-            c->launches += 2;
-            float *ga = b->gacc + b->gacc_off[l];
-            if (int rc = dg_bf16_wgrad_single(c, b->num_sms, b->dz_hi, b->x_hi, ga, m->n, cin_pad, li.cout, li.k)) return rc;
-            if (int rc = dg_bf16_wgrad_single(c, b->num_sms, b->dz_hi, b->x_lo, ga, m->n, cin_pad, li.cout, li.k)) return rc;
-            if (int rc = dg_bf16_wgrad_single(c, b->num_sms, b->dz_lo, b->x_hi, ga, m->n, cin_pad, li.cout, li.k)) return rc;
-        }
         if (l > 0) {   // input gradient through the conv, masked by the ReLU of the layer below (h_l > 0)
             const T32Geom &go = (l - 1) == 0 ? b->g_first : b->g3;
             T32Conv cp{};
@@ -498,6 +503,34 @@ int dg_tf32_backward(dg_model *m, const float *dz_top) {
             cp.mode = 1;
             if (int rc = t32_launch_conv(m, cp)) return rc;
         }
+    }
+    // ---- weight gradients: bf16 hi / lo splits of every layer's dZ and X, then hi*hi + hi*lo + lo*hi as "layers" of persistent launches
+    // of the bf16 weight-gradient kernel (15 products = 5 layers per launch for the 3x3 layers; the first layer on its own)
+    for (int l = L - 2; l >= 0; --l) {
+        const LayerInfo &li = m->layers[l];
+        const T32Geom &g = l == 0 ? b->g_first : b->g3;
+        const int cin_pad = l == 0 ? b->cin0_pad : li.cin;
+        t32_split_bf16_kernel<<<2 * b->num_sms, 256, 0, c->stream>>>(b->dzl[l], b->dz_hi[l], b->dz_lo[l], (size_t)m->n * (li.cout / 8) * g.rows, g.rows);
+        t32_split_bf16_kernel<<<2 * b->num_sms, 256, 0, c->stream>>>(l == 0 ? b->x0 : b->h[l], b->x_hi[l], b->x_lo[l], (size_t)m->n * (cin_pad / 8) * g.rows, g.rows);
+        c->launches += 2;
+    }
+    for (int l = L - 2; l >= 1;) {
+        const int nlay = std::min(l, 5);
+        const void *dz[15], *x[15];
+        float *ga[15];
+        int k = 0;
+        for (int j = 0; j < nlay; ++j) {
+            const int lj = l - j;
+            const void *dzs[3] = {b->dz_hi[lj], b->dz_hi[lj], b->dz_lo[lj]}, *xs[3] = {b->x_hi[lj], b->x_lo[lj], b->x_hi[lj]};
+            for (int q = 0; q < 3; ++q, ++k) { dz[k] = dzs[q]; x[k] = xs[q]; ga[k] = b->gacc + b->gacc_off[lj]; }
+        }
+        if (int rc = dg_bf16_wgrad_multi(c, b->num_sms, k, dz, x, ga, m->n, m->C, m->C, 3)) return rc;
+        l -= nlay;
+    }
+    {
+        const void *dz[3] = {b->dz_hi[0], b->dz_hi[0], b->dz_lo[0]}, *x[3] = {b->x_hi[0], b->x_lo[0], b->x_hi[0]};
+        float *ga[3] = {b->gacc, b->gacc, b->gacc};
+        if (int rc = dg_bf16_wgrad_multi(c, b->num_sms, 3, dz, x, ga, m->n, b->cin0_pad, m->layers[0].cout, m->layers[0].k)) return rc;
     }
     if (int rc = dg_launch_wgrad_finalize(c, b->fin_table, L - 1, c->stream)) return rc;
     DG_CUDA(cudaGetLastError());

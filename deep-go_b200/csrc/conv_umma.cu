@@ -2162,28 +2162,41 @@ int dg_bf16_dp_prepare(dg_model *m) {
     return 0;
 }
 
-// One layer's weight gradient with the bf16 tensor-core kernel, for callers outside this path (conv_tf32.cu feeds it hi/lo splits of
-// fp32 images): dz [n][cout/8][R][8], x [n][cin_pad/8][R][8] in the geometry of a k x k layer, partial tiles ADDED into
-// gacc [tap][cin_pad/4][cout][4].
-int dg_bf16_wgrad_single(dg_ctx *c, int num_sms, const void *dz, const void *x, float *gacc, int n, int cin_pad, int cout, int ksize) {
+// Weight gradients with the bf16 tensor-core kernel for callers outside this path (conv_tf32.cu feeds it hi/lo splits of fp32
+// images): `nl` (<= 16) products of one shape in ONE persistent launch -- product j adds dz[j]^T x[j] per tap into gacc[j]
+// ([tap][cin_pad/4][cout][4]; several products may name the same block).  dz [n][cout/8][R][8], x [n][cin_pad/8][R][8] in the
+// geometry of a k x k layer.  The layer groups are chosen by a small cost model: phases x (units per CTA + a drain).
+int dg_bf16_wgrad_multi(dg_ctx *c, int num_sms, int nl, const void *const *dz, const void *const *x, float *const *gacc, int n, int cin_pad, int cout, int ksize) {
+    DG_REQUIRE(nl >= 1 && nl <= WG_MAX_LAYERS, "weight gradient: %d products in one launch (1..%d)", nl, WG_MAX_LAYERS);
     const Geom g = geom_for(ksize);
     WgradPlan w;
     if (int rc = wgrad_plan(num_sms, cin_pad, cout, ksize, g, w)) return rc;
+    DG_REQUIRE(w.rp == 128, "weight gradient: 128-row stages expected");
     static bool attr_set[64] = {false};
     if (c->dev < 64 && !attr_set[c->dev]) {
         DG_CUDA(cudaFuncSetAttribute(wgrad_umma_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
         attr_set[c->dev] = true;
     }
+    const int panels = g.ntiles * 128 / w.rp, units = n * panels, per_row = num_sms / w.combos;
+    int best_g = 1, best_st = w.splits;
+    double best_t = 1e30;
+    for (int G = 1; G <= nl; ++G) {
+        if (nl % G) continue;
+        const int st = G == 1 ? w.splits : per_row / (G * panels) * (G * panels);
+        if (st < G * panels && G > 1) continue;
+        if (units < st / G) continue;
+        const double t = (double)(nl / G) * ((units * G + st - 1) / st + 5.0);      // microseconds, roughly: 1 per unit, 5 per drain + refill
+        if (t < best_t) { best_t = t; best_g = G; best_st = st; }
+    }
     WgradParams wp{};
-    wp.dz[0] = (const bf16 *)dz; wp.x[0] = (const bf16 *)x; wp.gacc[0] = gacc; wp.gab[0] = nullptr;
-    wp.scratch = nullptr; wp.nl = 1;
+    for (int j = 0; j < nl; ++j) { wp.dz[j] = (const bf16 *)dz[j]; wp.x[j] = (const bf16 *)x[j]; wp.gacc[j] = gacc[j]; wp.gab[j] = nullptr; }
+    wp.scratch = nullptr; wp.nl = nl;
     wp.n = n; wp.cin = cin_pad; wp.cout = cout;
     wp.R = g.rows; wp.pitch = g.pitch; wp.pad = g.pad; wp.ksize = ksize; wp.first = g.first; wp.ntiles = g.ntiles;
-    wp.ngroups = 1;
-    wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = w.splits; wp.nstages = w.nstages;
-    DG_REQUIRE(w.rp == 128, "weight gradient: 128-row stages expected");
+    wp.ngroups = best_g;
+    wp.nb = w.nb; wp.n_mblk = w.n_mblk; wp.n_nblk = w.n_nblk; wp.splits = best_st / best_g; wp.nstages = w.nstages;
     { dg_prof_scope _ps(c, DG_K_WGRAD);
-    DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<128>, dim3(w.combos * w.splits), dim3(384), w.smem, c->stream, wp)); }
+    DG_CUDA(dg_launch_pdl(wgrad_umma_kernel<128>, dim3(w.combos * best_st), dim3(384), w.smem, c->stream, wp)); }
     c->launches++;
     return 0;
 }

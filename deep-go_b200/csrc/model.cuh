@@ -10,7 +10,7 @@ struct FinalizeLayer {
     const float *gacc; float *gW; int cin_true, cin, cout, ksize;
     const float *gab; float *ga, *gb; int pitch, pad, first;      // bias gradients accumulated by the weight-gradient kernel (gab may be NULL)
 };
-int dg_bf16_wgrad_single(dg_ctx *c, int num_sms, const void *dz_bf16, const void *x_bf16, float *gacc, int n, int cin_pad, int cout, int ksize);   // conv_umma.cu
+int dg_bf16_wgrad_multi(dg_ctx *c, int num_sms, int nl, const void *const *dz_bf16, const void *const *x_bf16, float *const *gacc, int n, int cin_pad, int cout, int ksize);   // conv_umma.cu
 int dg_launch_wgrad_finalize(dg_ctx *ctx, const FinalizeLayer *table_dev, int nlayers, cudaStream_t st);    // conv_umma.cu
 
 struct dg_model {
