@@ -83,7 +83,7 @@ def _golden_batch(n, step=7):
     return dict(raw=g["raw"][idx], player=pl, rank=g["ranks"][idx, pl - 1], x=g["x"][idx], y=g["y"][idx])
 
 
-@pytest.mark.parametrize("prec,world", [(0, 2), (1, 2), (1, 8)])
+@pytest.mark.parametrize("prec,world", [(0, 2), (1, 2), (2, 2), (1, 8)])
 def test_multi_device_context_matches_one_gpu(prec, world):
     """dg_ctx_create_multi: one model handle over `world` devices trains like one GPU on the whole batch -- same log-probs, same
     loss, same top-1 errors, parameters within the summation-order tolerance; uneven split (n % world != 0) included."""
@@ -119,6 +119,18 @@ def test_multi_device_context_matches_one_gpu(prec, world):
         l1, lm = one.train_step(0.05), multi.train_step(0.05)
         assert abs(l1 - lm) < tol
     assert np.abs(one.get_params() - multi.get_params()).max() < tol
+    # c5 inference over the replicas: 8-fold symmetry-averaged probabilities and their argmax for the whole batch
+    for m in (one, multi):
+        m.set_batch_raw(b["raw"], b["player"], b["rank"], None, b["x"], b["y"])
+    (p1, a1), (pm, am) = one.predict_sym8(), multi.predict_sym8()
+    assert np.abs(p1 - pm).max() < 5e-3 and np.allclose(pm.sum(1), 1.0, atol=1e-3)
+    assert (a1 == am).mean() >= 0.9
+    # the reference's own staging (planes + targets) splits the same way
+    from oracle import encode
+    x, t = encode.load_minibatch(b["raw"], b["player"], b["rank"], b["x"], b["y"], None, np.float32)
+    for m in (one, multi):
+        m.set_batch_planes(x, t)
+    assert abs(one.eval_batch()[1] - multi.eval_batch()[1]) < 5e-3
     with pytest.raises(Exception):                               # fewer positions than devices
         multi.set_batch_raw(b["raw"][:world - 1], b["player"][:world - 1], b["rank"][:world - 1])
 
