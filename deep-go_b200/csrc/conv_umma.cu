@@ -2378,6 +2378,9 @@ int dg_bf16_backward(dg_model *m, float scale) {
     // layer 0 on its own
     struct WgLaunch { int l, nl, ngroups, grid; WgradPlan w; };
     std::vector<WgLaunch> wl;
+    // (Measured and dropped: the top conv layer's weight gradient on the 20 SMs that have no position during the input-gradient chain,
+    // on the side stream -- the persistent launch then has 9 layers in 3 phases and is 5 us shorter, but the step as a whole came
+    // out 10 us LONGER: the side kernel delays the chain and the join in front of the SGD kernel.)
     for (int l = m->L - 2; l >= 0;) {
         const LayerInfo &li = m->layers[l];
         const Geom &g = l == 0 ? b->g_first : b->g3;
@@ -2390,14 +2393,21 @@ int dg_bf16_backward(dg_model *m, float scale) {
         // panel index (splits per group a multiple of the panels).  Default: TWO PHASES (G = layers / 2): a CTA accumulates a layer over
         // many units and drains only twice, and the drain's red.global traffic (the partial tile of every CTA) drops with the number
         // of CTAs per layer: 10 layers in 5 groups of 27 CTAs measured 104 us against 113 us for 2 groups of 72 CTAs, 13 SMs idle
-        // notwithstanding.  DG_WG_GROUPS overrides.
+        // notwithstanding.  DG_WG_GROUPS forces a count.
         static const int env_groups = [] { const char *e = getenv("DG_WG_GROUPS"); return e ? atoi(e) : 0; }();
-        const int want_groups = env_groups > 0 ? env_groups : (q.nl % 2 == 0 ? q.nl / 2 : 1);
         q.ngroups = 1;
-        if (!b->deterministic && q.nl >= 2 && want_groups >= 2 && q.nl % want_groups == 0) {
-            const int per_row = b->num_sms / q.w.combos;                                  // CTAs a kernel row can have
-            const int st = per_row / (want_groups * panels_l) * (want_groups * panels_l);   // .. dealt evenly to the groups
-            if (st >= want_groups * panels_l && m->n * panels_l >= st / want_groups) { q.ngroups = want_groups; q.w.splits = st; }
+        if (!b->deterministic && q.nl >= 2) {
+            // G among the divisors of the layer count by a small cost model: phases x (units per CTA, ~1 us each, + ~5 us per drain and refill)
+            const int per_row = b->num_sms / q.w.combos, units = m->n * panels_l;         // CTAs a kernel row can have; split-K units per layer and row
+            double best_t = 1e30;
+            for (int G = 1; G <= q.nl; ++G) {
+                if (q.nl % G || (env_groups > 0 && G != env_groups)) continue;
+                const int st = G == 1 ? q.w.splits : per_row / (G * panels_l) * (G * panels_l);   // .. dealt evenly to the groups
+                if ((G > 1 && st < G * panels_l) || units < st / G) continue;
+                const double t = (double)(q.nl / G) * ((units * G + st - 1) / st + 5.0);
+                if (t < best_t) { best_t = t; q.ngroups = G; }
+            }
+            if (q.ngroups > 1) q.w.splits = per_row / (q.ngroups * panels_l) * (q.ngroups * panels_l);
         }
         q.grid = q.w.combos * q.w.splits;
         wl.push_back(q);
