@@ -138,9 +138,10 @@ def test_multi_device_context_matches_one_gpu(prec, world):
 @pytest.mark.parametrize("prec", [0, 1])
 def test_experiment_numgpus_2(tmp_path, capsys, prec):
     """Experiment{useCuda = true, numGPUs = 2}:run{iters} (experiments.lua:97-103) equals the one-GPU run on the same minibatches.
-    fp32: costs to 2e-3, parameters to 1e-2 (measured 3e-3; 20 steps at rate 0.05 on three positions overfit fast, and the order of the gradient sums differs).  bf16: 20 steps at rate 0.05 on three positions drive the cost from 5.9 to 1.1, and the two runs differ in the
-    order their gradient sums are formed, so the trajectories drift apart by a few percent; the engine-level test above holds
-    the bf16 path to 2e-3 over 3 steps."""
+    A small rate (0.005) on purpose: at the localtest rate of 0.05 twenty steps on three positions drive the cost from 5.9 to 1 and
+    the trajectory amplifies the order of the floating-point gradient sums (atomics) to percents -- two runs of the SAME one-GPU
+    configuration then differ by 4 % in their validation cost.  fp32: 2e-3; bf16: 2e-2 on the costs, 5e-2 on the late validation
+    cost (the engine-level test above holds the bf16 path to 2e-3 over 3 steps)."""
     entry.build()
     from deepgo_b200.host import engine, experiments
     if engine.device_count() < 2:
@@ -156,7 +157,7 @@ def test_experiment_numgpus_2(tmp_path, capsys, prec):
     runs = []
     for ngpu in (1, 2):
         e = experiments.basicGoExperiment.new(dict(useCuda=True, numGPUs=ngpu, data_root=str(root / "data"), validation_interval=20,
-                                                   validationSize=8, batchSize=6, precision=prec, rate=0.05))
+                                                   validationSize=8, batchSize=6, precision=prec, rate=0.005))
         e.init()
         assert len(e.model.ctx.devices) == ngpu
         rng = np.random.default_rng(9)
@@ -168,4 +169,4 @@ def test_experiment_numgpus_2(tmp_path, capsys, prec):
     if prec == 0:
         assert np.allclose(c1, c2, atol=2e-3) and np.allclose(v1, v2, atol=2e-3) and np.abs(p1 - p2).max() < 1e-2
     else:
-        assert np.allclose(c1, c2, rtol=5e-2) and np.allclose(v1, v2, rtol=2.5e-1)      # the late validation cost sits at the end of the drift
+        assert np.allclose(c1, c2, rtol=2e-2) and np.allclose(v1, v2, rtol=5e-2)
