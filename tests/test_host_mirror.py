@@ -139,7 +139,7 @@ def test_localtest_replay(host, tmp_path, capsys, precision):
 
 def _experiment(host, root, tmp_path, **kw):
     ex = host["experiments"]
-    opts = dict(useCuda=False, data_root=str(root / "data"), validation_interval=20, validationSize=10, batchSize=4, precision=0, rate=0.05)
+    opts = dict(useCuda=False, data_root=str(root / "data"), validation_interval=20, validationSize=10, batchSize=4, precision=0, rate=0.01)
     opts.update(kw)
     e = ex.basicGoExperiment.new(opts)
     os.chdir(tmp_path)
@@ -199,7 +199,7 @@ def test_train_bookkeeping_equals_oracle_replay(host, tmp_path, capsys, separate
     tnames = [[e.datasets["train"].generate_random_filename() for _ in range(B)] for _ in range(iters)]
     vx, vt = _oracle_batch_of(host, vnames, root)
     p = torch.from_numpy(flat).double()
-    rate, avg, want, vwant = 0.05, None, [], []
+    rate, avg, want, vwant = 0.01, None, [], []
     for it in range(1, iters + 1):
         x, t = _oracle_batch_of(host, tnames[it - 1], root)
         cost, g, _ = net.loss_and_grads(p, torch.from_numpy(x), t, e.numLayers, e.channelSize)
@@ -233,11 +233,11 @@ def test_checkpoint_resume_and_repeated_run(host, tmp_path, capsys):
     e2 = host["experiments"].Experiment.load(fn)
     assert e2.iterations == 20 and e2.numLayers == 3 and e2.channelSize == 64 and e2.batchSize == 4 and e2.validation_costs == e.validation_costs
     assert np.array_equal(e2.modelParameters.numpy(), e.modelParameters.numpy())
-    assert e2.optimizer.rate == e.optimizer.rate and e2.optimizer.rate < 0.05
+    assert e2.optimizer.rate == e.optimizer.rate and e2.optimizer.rate < 0.01
     r, _ = repeated.repeated(fn, gpu=1, num=7, iters=10, base=str(root))
     assert r.id == "repeatedRun7" and r.iterations == 30
-    assert abs(r.optimizer.rate - 0.05 * (1 - 1e-7) ** 10) < 1e-15          # the loaded run's decayed rate was dropped (repeated.lua:17)
-    assert "experiment rate 0.05" in capsys.readouterr().out
+    assert abs(r.optimizer.rate - 0.01 * (1 - 1e-7) ** 10) < 1e-15          # the loaded run's decayed rate was dropped (repeated.lua:17)
+    assert "experiment rate 0.01" in capsys.readouterr().out
     assert not np.array_equal(r.modelParameters.numpy(), e.modelParameters.numpy())
     # a checkpoint in the reference's own format goes through the same door
     from tests.test_checkpoint import write_reference_model
