@@ -593,11 +593,13 @@ extern "C" int dg_train_step(dg_model *m, float rate, float *loss_out) {
     DG_REQUIRE(m->n > 0, "dg_train_step: no batch staged");
     if (m->bf) if (int rc = dg_bf16_dp_prepare(m)) return rc;
     static const bool no_graph = getenv("DG_NO_GRAPH") != nullptr || getenv("DG_TIMELINE") != nullptr;
-    // with data parallelism the NCCL allreduce is captured too (the communication stream joins the capture through events)
+    // with data parallelism the gradient exchange is captured too: the peer-memory kernel is just another node; the NCCL fallback's
+    // communication stream joins the capture through events
     static const bool no_dp_graph = getenv("DG_NO_DP_GRAPH") != nullptr;
     const bool use_graph = m->prec == DG_PREC_BF16 && (c->world == 1 || !no_dp_graph) && !c->prof_on && !no_graph;
     if (use_graph) {
-        // the ~50 launches and the cross-stream event edges of a step are captured once per batch size and replayed
+        // the launches and the cross-stream event edges of a step (10 nodes for the chained bf16 net) are captured once per batch size
+        // and replayed
         const int rs = m->rate_slot++ & 7;
         DG_CUDA(cudaEventSynchronize(m->ev_rate[rs]));      // the copy that last read this slot is done (8 steps ago)
         m->h_rate[rs] = rate;
