@@ -1544,7 +1544,7 @@ __global__ void __launch_bounds__(512) encode_blocked_kernel(const uint8_t *__re
         unsigned long long m = 0;
         if (y >= 0 && y < DG_BOARD) m = dg_plane_bits(rec_s + shift, dg_src_point_d(x * DG_BOARD + y, sy), pl, rk);      // x is on the board for every row in range
 #pragma unroll
-        for (int c = 0; c < 6; ++c) *reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8) = dg_plane_chunk(m, c);
+        for (int c = 0; c < 6; ++c) __stcs(reinterpret_cast<uint4 *>(out + (((size_t)n * 6 + c) * R + rho) * 8), dg_plane_chunk(m, c));      // written once, read by another kernel: streaming stores
     }
 }
 
