@@ -294,6 +294,7 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     DG_CUDA(cudaMalloc(&m->d_errors, 4));
     DG_CUDA(cudaMalloc(&m->d_rate, 4));
     DG_CUDA(cudaMallocHost(&m->h_rate, 8 * 4));
+    DG_CUDA(cudaMallocHost(&m->h_res, 2 * 4));
     for (int i = 0; i < 8; ++i) DG_CUDA(cudaEventCreateWithFlags(&m->ev_rate[i], cudaEventDisableTiming));
     m->act.assign(num_layers + 1, nullptr);
     DG_CUDA(cudaMalloc(&m->act[0], B * in_planes * DG_POINTS * 4));
@@ -324,7 +325,7 @@ extern "C" int dg_model_destroy(dg_model *m) {
     cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
     if (m->h_meta) { cudaFreeHost(m->h_meta); for (int i = 0; i < 4; ++i) cudaEventDestroy(m->ev_meta[i]); }
     cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
-    cudaFree(m->d_loss); cudaFree(m->d_errors); cudaFree(m->d_rate); cudaFreeHost(m->h_rate);
+    cudaFree(m->d_loss); cudaFree(m->d_errors); cudaFree(m->d_rate); cudaFreeHost(m->h_rate); cudaFreeHost(m->h_res);
     if (m->step_graph) cudaGraphExecDestroy(m->step_graph);
     for (int i = 0; i < 8; ++i) if (m->ev_rate[i]) cudaEventDestroy(m->ev_rate[i]);
     dg_ctx *c = m->ctx;
@@ -531,9 +532,12 @@ int dg_backward_impl(dg_model *m) {
 int dg_read_loss(dg_model *m, float *loss_out, int *errors_out) {
     dg_ctx *c = m->ctx;
     if (!m->loss_reduced) if (int rc = dg_launch_loss_reduce(c, m->d_loss_n, m->d_argmax, m->d_targets, m->n, m->d_loss, m->d_errors)) return rc;
-    if (loss_out) DG_CUDA(cudaMemcpyAsync(loss_out, m->d_loss, 4, cudaMemcpyDeviceToHost, c->stream));
-    if (errors_out) DG_CUDA(cudaMemcpyAsync(errors_out, m->d_errors, 4, cudaMemcpyDeviceToHost, c->stream));
+    // through a pinned word pair: a copy into the caller's pageable memory goes through the driver's own staging and blocks twice
+    if (loss_out) DG_CUDA(cudaMemcpyAsync(m->h_res, m->d_loss, 4, cudaMemcpyDeviceToHost, c->stream));
+    if (errors_out) DG_CUDA(cudaMemcpyAsync(m->h_res + 1, m->d_errors, 4, cudaMemcpyDeviceToHost, c->stream));
     DG_CUDA(cudaStreamSynchronize(c->stream));
+    if (loss_out) *loss_out = m->h_res[0];
+    if (errors_out) memcpy(errors_out, m->h_res + 1, 4);
     return 0;
 }
 

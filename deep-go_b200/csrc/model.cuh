@@ -39,6 +39,7 @@ struct dg_model {
     long long step_graph_launches = 0;
     // rate for the graph's SGD node: device scalar, fed from a ring of pinned slots (a slot is rewritten only after the copy that
     // reads it has completed: steps that return without a host sync would otherwise see the next step's rate)
+    float *h_res = nullptr;            // pinned {loss, error count}: where the step's scalars land before they go to the caller
     float *d_rate = nullptr, *h_rate = nullptr;
     cudaEvent_t ev_rate[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     unsigned rate_slot = 0;
