@@ -1997,13 +1997,11 @@ int dg_bf16_create(dg_model *m) {
             tab[l].cin_true = li.cin; tab[l].cin = b->ops[l].cin_pad; tab[l].cout = li.cout; tab[l].ksize = li.k;
         }
         std::vector<FinalizeLayer> ft(L - 1);
-        size_t goff = 0;
         for (int l = 0; l < L - 1; ++l) {
             const LayerInfo &li = m->layers[l];
             ft[l].gacc = nullptr; ft[l].gW = m->grads + li.offW; ft[l].cin_true = li.cin; ft[l].cin = b->ops[l].cin_pad; ft[l].cout = li.cout; ft[l].ksize = li.k;
             const Geom &gl = l == 0 ? b->g_first : b->g3;
             ft[l].gab = nullptr; ft[l].ga = m->grads + li.offA; ft[l].gb = m->grads + li.offB; ft[l].pitch = gl.pitch; ft[l].pad = gl.pad; ft[l].first = gl.first;
-            (void)goff;
         }
         b->fin_host = ft;
         std::vector<SgdPackLayer> sg(L);
