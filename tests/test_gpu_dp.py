@@ -39,7 +39,7 @@ dist.destroy_process_group()
 '''
 
 
-@pytest.mark.parametrize("prec,world,variant", [(0, 2, ""), (1, 2, ""), (1, 8, ""), (1, 2, "DG_DP_NCCL"), (1, 2, "DG_DP_PULL"), (1, 2, "DG_DP_WRITE")])
+@pytest.mark.parametrize("prec,world,variant", [(0, 2, ""), (1, 2, ""), (2, 2, ""), (1, 8, ""), (1, 2, "DG_DP_NCCL"), (1, 2, "DG_DP_PULL"), (1, 2, "DG_DP_WRITE")])
 def test_ranks_match_one_gpu(tmp_path, prec, world, variant):
     """variant: the exchange's opt-in alternatives (NCCL allreduce, reduce-scatter + pull, write-only) give the same result"""
     entry.build()
