@@ -263,6 +263,21 @@ int dg_model_layout(dg_model *m, int num_layers, int channel_size, int in_planes
     return 0;
 }
 
+// d_raw, d_player .. point into record buffer b
+static void select_record_buffer(dg_model *m, int b) {
+    const size_t B = (size_t)m->max_batch;
+    m->stage_cur = b;
+    m->d_raw = m->d_raw_buf[b];
+    m->d_player = m->d_meta_buf[b];
+    m->d_rank = m->d_player + B; m->d_sym = m->d_rank + B; m->d_x = m->d_sym + B; m->d_y = m->d_x + B; m->d_sym_keep = m->d_y + B;
+}
+// call after queueing an encode that reads the current record buffer: the next copy into that buffer waits for it
+int dg_model_mark_encoded(dg_model *m) {
+    DG_CUDA(cudaEventRecord(m->ev_enc[m->stage_cur], m->ctx->stream));
+    m->enc_recorded[m->stage_cur] = true;
+    return 0;
+}
+
 extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int in_planes, int k_first, int precision,
                                int max_batch, dg_model **out) {
     DG_REQUIRE(c && out, "dg_model_create: NULL argument");
@@ -283,9 +298,16 @@ extern "C" int dg_model_create(dg_ctx *c, int num_layers, int channel_size, int 
     DG_CUDA(cudaMalloc(&m->grads, m->P * 4));
     DG_CUDA(cudaMemsetAsync(m->params, 0, m->P * 4, c->stream));
     DG_CUDA(cudaMemsetAsync(m->grads, 0, m->P * 4, c->stream));
-    DG_CUDA(cudaMalloc(&m->d_raw, B * DG_RAW_PLANES * DG_POINTS));
-    DG_CUDA(cudaMalloc(&m->d_player, B * 6));
-    m->d_rank = m->d_player + B; m->d_sym = m->d_rank + B; m->d_x = m->d_sym + B; m->d_y = m->d_x + B; m->d_sym_keep = m->d_y + B;
+    for (int i = 0; i < 2; ++i) {
+        DG_CUDA(cudaMalloc(&m->d_raw_buf[i], B * DG_RAW_PLANES * DG_POINTS));
+        DG_CUDA(cudaMalloc(&m->d_meta_buf[i], B * 6));
+        DG_CUDA(cudaEventCreateWithFlags(&m->ev_copy[i], cudaEventDisableTiming));
+        DG_CUDA(cudaEventCreateWithFlags(&m->ev_enc[i], cudaEventDisableTiming));
+    }
+    DG_CUDA(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+    DG_CUDA(cudaMallocHost(&m->h_loss_ring, 4 * 4));
+    for (int i = 0; i < 4; ++i) DG_CUDA(cudaEventCreateWithFlags(&m->ev_loss[i], cudaEventDisableTiming));
+    select_record_buffer(m, 0);
     DG_CUDA(cudaMalloc(&m->d_targets, B * 4));
     DG_CUDA(cudaMalloc(&m->d_argmax, B * 4));
     DG_CUDA(cudaMalloc(&m->d_logp, B * DG_POINTS * 4));
@@ -322,7 +344,11 @@ extern "C" int dg_model_destroy(dg_model *m) {
     if (m->t32) dg_tf32_destroy(m);
     for (float *p : m->act) if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) if (m->dz[i]) cudaFree(m->dz[i]);
-    cudaFree(m->params); cudaFree(m->grads); cudaFree(m->d_raw); cudaFree(m->d_player);
+    cudaFree(m->params); cudaFree(m->grads);
+    for (int i = 0; i < 2; ++i) { cudaFree(m->d_raw_buf[i]); cudaFree(m->d_meta_buf[i]); if (m->ev_copy[i]) cudaEventDestroy(m->ev_copy[i]); if (m->ev_enc[i]) cudaEventDestroy(m->ev_enc[i]); }
+    if (m->copy_stream) { cudaStreamSynchronize(m->copy_stream); cudaStreamDestroy(m->copy_stream); }
+    if (m->h_loss_ring) cudaFreeHost(m->h_loss_ring);
+    for (int i = 0; i < 4; ++i) if (m->ev_loss[i]) cudaEventDestroy(m->ev_loss[i]);
     if (m->h_meta) { cudaFreeHost(m->h_meta); for (int i = 0; i < 4; ++i) cudaEventDestroy(m->ev_meta[i]); }
     cudaFree(m->d_targets); cudaFree(m->d_argmax); cudaFree(m->d_logp); cudaFree(m->d_loss_n);
     cudaFree(m->d_loss); cudaFree(m->d_errors); cudaFree(m->d_rate); cudaFreeHost(m->h_rate); cudaFreeHost(m->h_res);
@@ -405,7 +431,17 @@ extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uin
     if (int rc = check_records(player, rank, sym, n)) return rc;
     dg_ctx *c = m->ctx;
     DG_CUDA(cudaSetDevice(c->dev));
-    DG_CUDA(cudaMemcpyAsync(m->d_raw, raw, (size_t)n * DG_RAW_PLANES * DG_POINTS, cudaMemcpyHostToDevice, c->stream));
+    // The records go into the buffer the previous minibatch did NOT use, on the copy stream: a step that is still running on the
+    // context's stream (dg_train_step_begin) keeps its records, and the copy runs under it.  The copy waits for the last encode
+    // that read this buffer; the context's stream waits for the copy.  (With DG_FUSED_ENCODE the step graph itself reads the
+    // records through pointers fixed at capture: one buffer, the context's stream.)
+    const bool two = !dg_bf16_input_mode_fused();
+    cudaStream_t cs = two ? m->copy_stream : c->stream;
+    if (two) {
+        select_record_buffer(m, m->stage_cur ^ 1);
+        if (m->enc_recorded[m->stage_cur]) DG_CUDA(cudaStreamWaitEvent(cs, m->ev_enc[m->stage_cur], 0));
+    }
+    DG_CUDA(cudaMemcpyAsync(m->d_raw, raw, (size_t)n * DG_RAW_PLANES * DG_POINTS, cudaMemcpyHostToDevice, cs));
     m->n = n; m->have_raw = true; m->forward_done = false;
     m->have_targets = x != nullptr;
     if (x)
@@ -426,15 +462,19 @@ extern "C" int dg_model_set_batch_raw(dg_model *m, const uint8_t *raw, const uin
         memcpy(h, player, n); memcpy(h + B, rank, n);
         if (sym) memcpy(h + 2 * B, sym, n); else memset(h + 2 * B, 0, n);
         if (x) { memcpy(h + 3 * B, x, n); memcpy(h + 4 * B, y, n); }
-        DG_CUDA(cudaMemcpyAsync(m->d_player, h, x ? 4 * B + n : 2 * B + n, cudaMemcpyHostToDevice, c->stream));
-        DG_CUDA(cudaEventRecord(m->ev_meta[slot], c->stream));
+        DG_CUDA(cudaMemcpyAsync(m->d_player, h, x ? 4 * B + n : 2 * B + n, cudaMemcpyHostToDevice, cs));
+        DG_CUDA(cudaEventRecord(m->ev_meta[slot], cs));
+    }
+    if (two) {
+        DG_CUDA(cudaEventRecord(m->ev_copy[m->stage_cur], cs));
+        DG_CUDA(cudaStreamWaitEvent(c->stream, m->ev_copy[m->stage_cur], 0));
     }
     if (x) {
         // the bf16 path's encode kernel computes the labels as well (one launch less per batch)
         if (m->prec != DG_PREC_BF16 || dg_bf16_input_mode_fused()) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, n, m->d_targets)) return rc;
     }
-    if (m->prec != DG_PREC_BF16) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]);
-    return dg_bf16_stage_raw(m);
+    if (int rc = m->prec != DG_PREC_BF16 ? dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, n, m->act[0]) : dg_bf16_stage_raw(m)) return rc;
+    return dg_model_mark_encoded(m);
 }
 
 extern "C" int dg_model_encode_resident(dg_model *m) {
@@ -445,8 +485,8 @@ extern "C" int dg_model_encode_resident(dg_model *m) {
     DG_CUDA(cudaSetDevice(c->dev));
     m->forward_done = false;
     if (m->have_targets && (m->prec != DG_PREC_BF16 || dg_bf16_input_mode_fused())) if (int rc = dg_launch_labels(c, m->d_x, m->d_y, m->d_sym, m->n, m->d_targets)) return rc;
-    if (m->prec != DG_PREC_BF16) return dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, m->n, m->act[0]);
-    return dg_bf16_stage_raw(m);
+    if (int rc = m->prec != DG_PREC_BF16 ? dg_launch_encode_f32(c, m->d_raw, m->d_player, m->d_rank, m->d_sym, m->n, m->act[0]) : dg_bf16_stage_raw(m)) return rc;
+    return dg_model_mark_encoded(m);
 }
 
 extern "C" int dg_model_set_batch_planes(dg_model *m, const float *planes, const int32_t *targets0, int n) {
@@ -666,4 +706,37 @@ extern "C" int dg_eval_batch(dg_model *m, int *errors_out, float *cost_out) {
     DG_CUDA(cudaSetDevice(m->ctx->dev));
     if (int rc = dg_forward_impl(m)) return rc;
     return dg_read_loss(m, cost_out, errors_out);
+}
+
+// ---------------------------------------------------------------------------------------------
+// a step without the wait: begin queues eval() + optimizer:step and the read-back of the cost, result waits for THAT step
+// ---------------------------------------------------------------------------------------------
+int dgm_train_step_begin(dg_model *m, float rate);
+int dgm_train_step_result(dg_model *m, float *loss_out);
+
+extern "C" int dg_train_step_begin(dg_model *m, float rate) {
+    DG_REQUIRE(m, "dg_train_step_begin: model is NULL");
+    if (DG_MULTI(m)) return dgm_train_step_begin(m, rate);
+    DG_REQUIRE(m->loss_pending < 0, "dg_train_step_begin: the previous step's result has not been collected (dg_train_step_result)");
+    if (int rc = dg_train_step(m, rate, nullptr)) return rc;
+    dg_ctx *c = m->ctx;
+    if (!m->loss_reduced) {
+        if (int rc = dg_launch_loss_reduce(c, m->d_loss_n, m->d_argmax, m->d_targets, m->n, m->d_loss, m->d_errors)) return rc;
+        m->loss_reduced = true;
+    }
+    const int slot = m->loss_slot++ & 3;
+    DG_CUDA(cudaMemcpyAsync(m->h_loss_ring + slot, m->d_loss, 4, cudaMemcpyDeviceToHost, c->stream));
+    DG_CUDA(cudaEventRecord(m->ev_loss[slot], c->stream));
+    m->loss_pending = slot;
+    return 0;
+}
+
+extern "C" int dg_train_step_result(dg_model *m, float *loss_out) {
+    DG_REQUIRE(m && loss_out, "dg_train_step_result: NULL argument");
+    if (DG_MULTI(m)) return dgm_train_step_result(m, loss_out);
+    DG_REQUIRE(m->loss_pending >= 0, "dg_train_step_result: no step has been begun (dg_train_step_begin)");
+    DG_CUDA(cudaEventSynchronize(m->ev_loss[m->loss_pending]));
+    *loss_out = m->h_loss_ring[m->loss_pending];
+    m->loss_pending = -1;
+    return 0;
 }

@@ -39,6 +39,18 @@ struct dg_model {
     long long step_graph_launches = 0;
     // rate for the graph's SGD node: device scalar, fed from a ring of pinned slots (a slot is rewritten only after the copy that
     // reads it has completed: steps that return without a host sync would otherwise see the next step's rate)
+    // Record staging is double-buffered and copied on a stream of its own: while step k runs on the context's stream, the records
+    // of minibatch k+1 travel into the other buffer (dg_train_step_begin / dg_model_set_batch_raw / dg_train_step_result).
+    // d_raw, d_player .. d_y above always point into the buffer of the minibatch staged last.
+    uint8_t *d_raw_buf[2] = {nullptr, nullptr}, *d_meta_buf[2] = {nullptr, nullptr};
+    int stage_cur = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy[2] = {nullptr, nullptr}, ev_enc[2] = {nullptr, nullptr};    // copy into buffer b landed / last encode that read buffer b
+    bool enc_recorded[2] = {false, false};
+    float *h_loss_ring = nullptr;      // pinned, 4 slots: the loss of a step begun with dg_train_step_begin
+    cudaEvent_t ev_loss[4] = {nullptr, nullptr, nullptr, nullptr};
+    unsigned loss_slot = 0;
+    int loss_pending = -1;
     float *h_res = nullptr;            // pinned {loss, error count}: where the step's scalars land before they go to the caller
     float *d_rate = nullptr, *h_rate = nullptr;
     cudaEvent_t ev_rate[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -62,6 +74,7 @@ int dg_model_layout(dg_model *m, int num_layers, int channel_size, int in_planes
 int dg_forward_impl(dg_model *m);
 int dg_backward_impl(dg_model *m);
 int dg_read_loss(dg_model *m, float *loss_out, int *errors_out);
+int dg_model_mark_encoded(dg_model *m);     // an encode that reads the current record buffer has been queued on the context's stream
 int dg_bf16_dp_prepare_local(dg_model *const *kids, int n);   // conv_umma.cu
 
 // conv_tf32.cu

@@ -324,3 +324,24 @@ int dgm_predict_sym8(dg_model *m, float *probs_out, int32_t *argmax_out) {
     }
     return 0;
 }
+
+int dgm_train_step_begin(dg_model *m, float rate) {
+    DG_REQUIRE(m->have_targets && m->n > 0, "dg_train_step_begin: no batch with targets staged");
+    const bool fused = m->kids[0]->bf && dg_bf16_defers_grads(m->kids[0]);
+    DG_REQUIRE(fused, "dg_train_step_begin on a multi-device model needs the bf16 path (the other precisions sum gradients between separate calls)");
+    if (int rc = dg_bf16_dp_prepare_local(m->kids.data(), (int)m->kids.size())) return rc;
+    for (dg_model *k : m->kids) if (int rc = dg_train_step_begin(k, rate)) return rc;
+    m->forward_done = true;
+    return 0;
+}
+
+int dgm_train_step_result(dg_model *m, float *loss_out) {
+    double s = 0.0;
+    for (dg_model *k : m->kids) {
+        float l = 0.f;
+        if (int rc = dg_train_step_result(k, &l)) return rc;
+        s += (double)l * k->n;
+    }
+    *loss_out = (float)(s / m->n);
+    return 0;
+}

@@ -209,6 +209,15 @@ class Model:
         check(self.L.dg_train_step(self.h, rate, loss))
         return float(loss[0])
 
+    def train_step_begin(self, rate):
+        """queue eval() + optimizer:step; stage the next minibatch while it runs; collect the cost with train_step_result()"""
+        check(self.L.dg_train_step_begin(self.h, rate))
+
+    def train_step_result(self):
+        loss = ffi.new("float *")
+        check(self.L.dg_train_step_result(self.h, loss))
+        return float(loss[0])
+
     def argmax(self):
         out = np.empty(self.n, np.int32)
         check(self.L.dg_argmax(self.h, ffi.cast("int32_t *", out.ctypes.data)))

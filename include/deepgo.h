@@ -206,6 +206,13 @@ int dg_sgd_step(dg_model *m, float rate);
 /* eval() + optimizer:step fused (train.lua:111,131): zero grads, forward, NLL, backward,
  * [allreduce], SGD.  loss_out may be NULL (no host sync). */
 int dg_train_step(dg_model *m, float rate, float *loss_out);
+/* The same step without the wait (no counterpart in the reference, whose loop is synchronous, train.lua:106-131): _begin queues
+ * eval() + optimizer:step and the read-back of the cost and returns; _result waits for THAT step and returns its cost.  Between the
+ * two the caller may stage the next minibatch: dg_model_set_batch_raw copies on a second stream into the other of two record
+ * buffers, so the host->device copy of minibatch k+1 runs under step k (its encode and its step queue up behind step k).  One
+ * step may be outstanding. */
+int dg_train_step_begin(dg_model *m, float rate);
+int dg_train_step_result(dg_model *m, float *loss_out);
 /* preds:max(2) (train.lua:29): 0-based argmax of the last forward, int32[n] to host */
 int dg_argmax(dg_model *m, int32_t *out);
 /* eval_validation inner loop (train.lua:28-37): forward + top-1 errors + mean NLL of the staged batch */

@@ -172,3 +172,39 @@ def test_gradient_vector_after_fused_step(golden):
     assert np.array_equal(m.get_params(), flat.numpy().astype(np.float32))
     m.forward(False); m.zero_grads(); m.loss_backward()
     assert U.rel(m.get_grads(), g_sep) < 1e-4
+
+
+@pytest.mark.parametrize("prec", [0, 1, 2])
+def test_begin_result_pipeline_equals_synchronous_steps(golden, prec):
+    """dg_train_step_begin / dg_model_set_batch_raw (next minibatch, copied on the second stream into the other record buffer while
+    the step runs) / dg_train_step_result: the same losses and the same parameters as staging and stepping one after the other,
+    over six DIFFERENT minibatches of two sizes."""
+    from deepgo_b200.host import engine
+    from oracle import net
+    L, C = 4, 64
+    flat = net.init_params(L, C, 17, "he").numpy().astype(np.float32)
+    batches = [U.sample(golden, 9 if i % 2 else 12, 300 + i) for i in range(6)]
+    stage = lambda m, b: m.set_batch_raw(b["raw"], b["player"], b["rank"], b["sym"], b["x"], b["y"])
+    ms = engine.Model(U.ctx(), L, C, prec, max_batch=12); ms.set_params(flat)
+    want = []
+    for b in batches:
+        stage(ms, b)
+        want.append(ms.train_step(0.01))
+    mp = engine.Model(U.ctx(), L, C, prec, max_batch=12); mp.set_params(flat)
+    got = []
+    stage(mp, batches[0])
+    for i in range(len(batches)):
+        mp.train_step_begin(0.01)
+        if i + 1 < len(batches):
+            stage(mp, batches[i + 1])            # lands in the other buffer while step i runs
+        got.append(mp.train_step_result())
+    tol = 1e-5 if prec == 0 else 2e-3            # the gradients are summed by atomics: the order differs run to run, and six steps amplify it
+    assert np.allclose(got, want, atol=tol), (got, want)
+    assert np.abs(mp.get_params() - ms.get_params()).max() < (1e-5 if prec == 0 else 5e-3)
+    import deepgo_b200
+    mp.train_step_begin(0.0)
+    with pytest.raises(deepgo_b200.DeepGoError):         # one step may be outstanding
+        mp.train_step_begin(0.0)
+    mp.train_step_result()
+    with pytest.raises(deepgo_b200.DeepGoError):
+        mp.train_step_result()
