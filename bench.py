@@ -352,6 +352,14 @@ def run_ours(args, rank, local_rank, world):
     total_ms = max_over_ranks(total_ms)
     ms_per_step = total_ms / args.steps
     value = BATCH * world / (ms_per_step * 1e-3)
+    # ---------------- per-kernel times for the roofline (a few extra steps right after the timed region: the kernel is timed alone, at the same clocks) ----------------
+    # every rank runs them (the steps contain the gradient exchange); rank 0 reports
+    ctx.prof_begin()
+    for _ in range(5):
+        m.encode_resident(); m.train_step(rate, want_loss=False)
+    prof = ctx.prof_end()
+    barrier()
+
     # ---------------- end to end through the C ABI with host buffers ----------------
     pin = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy() for k, v in b.items()}
     for _ in range(3):
@@ -381,14 +389,6 @@ def run_ours(args, rank, local_rank, world):
     e2e_sync_value = BATCH * world * args.steps / e2e_sync_s
     h2d = BATCH * (9 * 361 + 5)
     assert np.isfinite(loss)
-
-    # ---------------- per-kernel times for the roofline (a few extra steps, after the timed region) ----------------
-    # every rank runs them (the steps contain the gradient exchange); rank 0 reports
-    ctx.prof_begin()
-    for _ in range(5):
-        m.encode_resident(); m.train_step(rate, want_loss=False)
-    prof = ctx.prof_end()
-    barrier()
 
     # ---------------- c4 (BASELINE config 4): 256 positions per GPU (global 2048 at N=8), and the strong-scaling point ----------------
     c4 = {}
