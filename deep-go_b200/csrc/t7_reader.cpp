@@ -115,15 +115,18 @@ struct Parser {
         }
         case 6: case 7: case 8: {
             // a Lua function (Experiment:new copies the prototype's methods into every instance, so a pickled experiment carries
-            // them): reference index, string.dump bytes, then the table of upvalues.  Skipped.
-            const int ref = i32();
-            if (memo.count(ref)) return memo[ref];
+            // them): [reference index -- tags 7 and 8 only; the older tag 6 has none,] string.dump bytes, then the upvalues.  Skipped.
+            int ref = -1;
+            if (tag != 6) {
+                ref = i32();
+                if (memo.count(ref)) return memo[ref];
+            }
             const int32_t nbytes = i32();
             if (nbytes < 0 || !need((size_t)nbytes)) { ok = false; return -1; }
             p += nbytes;
             nodes.push_back(n);
             const int self = (int)nodes.size() - 1;
-            memo[ref] = self;
+            if (tag != 6) memo[ref] = self;
             parse(depth + 1);
             return self;
         }

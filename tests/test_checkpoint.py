@@ -60,8 +60,11 @@ class T7Writer:
         self.i32(4); self.i32(self.index()); self.string("V 1"); self.string("torch.%sStorage" % cls)
         self.i64(len(st)); self.out += st.tobytes()
 
-    def function(self):
-        self.i32(8); self.i32(self.index())
+    def function(self, tag=8):
+        """tag 8 (and legacy 7): memoised like tables; tag 6, the older form, carries no index"""
+        self.i32(tag)
+        if tag != 6:
+            self.i32(self.index())
         dumped = b"\x1bLJ\x02fake bytecode"
         self.i32(len(dumped)); self.out += dumped
         self.table([])                                 # upvalues
@@ -76,6 +79,7 @@ def write_reference_model(path, params, cls, rate, decay, iterations):
     w.table([
         ("name", lambda: w.str_("basicGoExperiment")),
         ("new", w.function),                                          # Experiment:new copies the methods into the instance
+        ("init", lambda: w.function(6)), ("run", lambda: w.function(7)),
         ("useCuda", lambda: w.boolean(True)),
         ("kernels", lambda: w.table([(1, lambda: w.number(5)), (2, lambda: w.number(3)), (3, lambda: w.number(3))])),
         ("criterion", lambda: w.module("nn.ClassNLLCriterion", [("sizeAverage", lambda: w.boolean(True))])),
